@@ -1,0 +1,71 @@
+#!/usr/bin/env python3
+"""Generate tests/golden/*.npz by running the UNMODIFIED reference (oracle/_ref) in this container.
+
+/root/reference does not exist on the GPU box, so the reference's outputs on seeded inputs are
+committed as small fixtures.  Inputs are reproducible: weights = tools/make_synth_gguf.py (preset, seed 0),
+codes = default_rng(seed).integers(0, 12800, T), embedding = models/en_female.emb.gguf (copied into the
+fixture; 128 floats).  Each fixture records the weight sha256 so a drifting generator is detected.
+
+    python tools/gen_golden.py            # needs oracle/_ref built and /root/reference mounted
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+
+from make_synth_gguf import write_gguf  # noqa: E402
+from oracle.refbind import RefLib  # noqa: E402
+
+CASES = [  # (fixture, preset, T, codes seed)
+    ("tiny_T50", "tiny", 50, 42),
+    ("tiny_T1", "tiny", 1, 7),
+    ("tiny_T133", "tiny", 133, 9),
+    ("upsampler_tiny_T20", "upsampler_tiny", 20, 42),
+    ("default_T24", "default", 24, 42),
+    ("upsampler_T12", "upsampler", 12, 42),
+]
+
+
+def main():
+    import gguf
+
+    R = RefLib()
+    emb = np.array(gguf.GGUFReader("/root/reference/models/en_female.emb.gguf").tensors[0].data, dtype=np.float32)
+    out_dir = os.path.join(ROOT, "tests", "golden")
+    os.makedirs(out_dir, exist_ok=True)
+    np.save(os.path.join(out_dir, "en_female_emb.npy"), emb)
+    cache = {}
+    for name, preset, T, seed in CASES:
+        if preset not in cache:
+            path = f"/tmp/mio_golden_{preset}.gguf"
+            cache[preset] = (path, write_gguf(path, preset, 0)[0])
+        path, sha = cache[preset]
+        codes = np.random.default_rng(seed).integers(0, 12800, T).astype(np.int32)
+        h = R.open_decoder(path)
+        spec = R.decode_spec(h, codes, emb, n_threads=1, flash=0)
+        R.close_decoder(h)
+        ctx = R.open_context(path)
+        audio, sr = R.synthesize(ctx, codes, emb, n_threads=1, flash=0)
+        R.close_context(ctx)
+        np.savez_compressed(os.path.join(out_dir, name + ".npz"), preset=preset, weights_sha256=sha, codes=codes,
+                            spec=spec, audio=audio, sample_rate=sr)
+        print(name, spec.shape, audio.shape, sr, float(np.abs(audio).max()))
+    # iSTFT-only fixture: the reference's embd_to_audio on BASELINE config-3 style spectra
+    rng = np.random.default_rng(7)
+    for n_fft, hop, frames in ((1920, 480, 12), (392, 98, 30), (120, 30, 5), (2048, 512, 3), (1280, 320, 4)):
+        nf = n_fft // 2 + 1
+        spec = np.concatenate([rng.normal(-2, 1, (frames, nf)), rng.uniform(-np.pi, np.pi, (frames, nf))], 1)
+        spec = spec.astype(np.float32)
+        spec[0, 0] = 6.0  # exercises the magnitude clip at 100
+        audio = R.istft(spec, n_fft, hop, 1)
+        np.savez_compressed(os.path.join(out_dir, f"istft_{n_fft}_{hop}.npz"), spec=spec, audio=audio,
+                            n_fft=n_fft, hop=hop)
+        print("istft", n_fft, hop, audio.shape)
+
+
+if __name__ == "__main__":
+    main()
