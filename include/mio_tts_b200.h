@@ -1,0 +1,203 @@
+/* mio_tts_b200.h -- C ABI of libmio_tts_b200.so, the B200-native MioCodec decode + iSTFT library.
+ *
+ * Drop-in boundary: every `mio_tts_*` entry point below has the name, argument order, ownership rules and
+ * error strings of the function it replaces in the reference's public header
+ * /root/reference/src/mio-tts-lib.h (cited per declaration as lib.h:LINE; implementation cited as
+ * lib.cpp:LINE = /root/reference/src/mio-tts-lib.cpp).  The header is self-contained: the three llama.h
+ * types the reference header pulls in are restated here with identical layout
+ * (/root/reference/llama.cpp/include/llama.h: llama_token = int32_t; enum llama_flash_attn_type
+ * {AUTO=-1, DISABLED=0, ENABLED=1} :183-187; struct llama_vocab is opaque).
+ *
+ * Conventions kept from the reference: functions return bool (NULL for constructors) and write a
+ * truncated message into err[err_size] on failure, never throw; out-buffers are owned by the caller and
+ * MUST be released with the matching mio_tts_*_free; inputs are borrowed for the duration of the call;
+ * all functions may be called from arbitrary threads.
+ *
+ * `mio_tts_b200_*` entry points are extensions the reference does not have (it has no batch API and its
+ * iSTFT is a file-static function): batched synthesis, the stage-level hooks the parity tests bind, and
+ * the resident-input timing hooks bench.py binds.
+ */
+#ifndef MIO_TTS_B200_H
+#define MIO_TTS_B200_H
+
+#include <stdbool.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(_WIN32)
+#define MIO_B200_API
+#else
+#define MIO_B200_API __attribute__((visibility("default")))
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifndef LLAMA_H            /* restated llama.h types (only when llama.h is not already included) */
+typedef int32_t llama_token;
+struct llama_vocab;
+enum llama_flash_attn_type {
+    LLAMA_FLASH_ATTN_TYPE_AUTO = -1,
+    LLAMA_FLASH_ATTN_TYPE_DISABLED = 0,
+    LLAMA_FLASH_ATTN_TYPE_ENABLED = 1,
+};
+#endif
+
+struct mio_tts_context;    /* lib.h:17 */
+struct mio_tts_vocab_map;  /* lib.h:18 */
+
+struct mio_tts_params {    /* lib.h:20-25 (by value) */
+    int32_t n_threads;                 /* ignored: there is no CPU path */
+    float max_reference_seconds;
+    enum llama_flash_attn_type wavlm_flash_attn_type;
+    enum llama_flash_attn_type miocodec_flash_attn_type;   /* ignored: attention is always the banded kernel */
+};
+
+/* lib.h:27, lib.cpp:805-812 */
+MIO_B200_API struct mio_tts_params mio_tts_default_params(void);
+
+/* lib.h:29-33, lib.cpp:814-848.  Loads the MioCodec GGUF (unchanged weight layout) and uploads re-tiled
+ * weights to the device chosen by MIO_TTS_BACKEND_DEVICE ("CUDA<n>", default CUDA0).  `wavlm_model` is
+ * accepted and remembered but not loaded (reference-audio embedding extraction is not part of this path). */
+MIO_B200_API struct mio_tts_context * mio_tts_init_from_file(const char * model_vocoder, const char * wavlm_model,
+                                                             char * err, size_t err_size);
+
+/* lib.h:36-39, lib.cpp:850-863.  Shares the device weights; unlike the reference the clone gets its own
+ * stream and workspace, so clones decode concurrently. */
+MIO_B200_API struct mio_tts_context * mio_tts_context_clone(const struct mio_tts_context * ctx, char * err,
+                                                            size_t err_size);
+
+/* lib.h:41, lib.cpp:865-867 */
+MIO_B200_API void mio_tts_free(struct mio_tts_context * ctx);
+
+/* lib.h:43-45, lib.cpp:869-885 */
+MIO_B200_API bool mio_tts_context_is_dynamic_global(const struct mio_tts_context * ctx);
+MIO_B200_API int32_t mio_tts_context_sample_rate(const struct mio_tts_context * ctx);
+MIO_B200_API int32_t mio_tts_context_samples_per_token(const struct mio_tts_context * ctx);
+
+/* lib.h:46-50, lib.cpp:887-915.  backend_name: "CUDA<n>" selects GPU n (weights move there), NULL/"" keeps
+ * the current device, "CPU" fails ("no CPU fallback"): the reference's ggml device names map to ordinals. */
+MIO_B200_API bool mio_tts_context_set_backend_device(struct mio_tts_context * ctx, const char * backend_name,
+                                                     char * err, size_t err_size);
+
+/* lib.h:52-57, lib.cpp:917-938.  Needs libllama's llama_tokenize / llama_token_to_piece in the process
+ * (resolved with dlsym at call time, as when loaded into llama-tts-mio / mio-tts-server). */
+MIO_B200_API struct mio_tts_vocab_map * mio_tts_vocab_map_init(const struct llama_vocab * vocab, char * err,
+                                                               size_t err_size);
+MIO_B200_API void mio_tts_vocab_map_free(struct mio_tts_vocab_map * map);
+
+/* lib.h:59-66, lib.cpp:940-985 */
+MIO_B200_API bool mio_tts_tokens_to_codes(const struct mio_tts_vocab_map * map, const llama_token * tokens,
+                                          size_t n_tokens, int32_t ** codes_out, size_t * n_codes_out, char * err,
+                                          size_t err_size);
+/* lib.h:71-74, lib.cpp:987-1000 */
+MIO_B200_API bool mio_tts_token_to_code(const struct mio_tts_vocab_map * map, llama_token token, int32_t * code_out);
+
+/* lib.h:76-90, lib.cpp:225-286, 1002-1044: text file, one code per token, "<|s_N|>" tolerated */
+MIO_B200_API bool mio_tts_codes_load(const char * path, int32_t ** codes_out, size_t * n_codes_out, char * err,
+                                     size_t err_size);
+MIO_B200_API bool mio_tts_codes_save(const char * path, const int32_t * codes, size_t n_codes, char * err,
+                                     size_t err_size);
+MIO_B200_API void mio_tts_codes_free(int32_t * codes);
+
+/* lib.h:92-99, lib.cpp:1046-1125.  Not on the decode path (WavLM + global encoder):
+ * fails with the reference's "WavLM model is not loaded" class of errors. */
+MIO_B200_API bool mio_tts_reference_to_embedding(struct mio_tts_context * ctx, const char * reference_audio,
+                                                 struct mio_tts_params params, float ** embedding_out,
+                                                 size_t * n_embedding_out, char * err, size_t err_size);
+
+/* lib.h:101-115, lib.cpp:288-413, 1127-1180: GGUF with one F32 tensor "mio.global_embedding" */
+MIO_B200_API bool mio_tts_embedding_load_gguf(const char * path, float ** embedding_out, size_t * n_embedding_out,
+                                              char * err, size_t err_size);
+MIO_B200_API bool mio_tts_embedding_save_gguf(const char * path, const float * embedding, size_t n_embedding,
+                                              char * err, size_t err_size);
+MIO_B200_API void mio_tts_embedding_free(float * embedding);
+
+/* lib.h:117-128, lib.cpp:1182-1323: codes + speaker embedding -> waveform (decode, iSTFT, peak normalise).
+ * *audio_out is a pinned host buffer from the library's result pool: release it with mio_tts_audio_free. */
+MIO_B200_API bool mio_tts_synthesize(struct mio_tts_context * ctx, const int32_t * codes, size_t n_codes,
+                                     const float * embedding, size_t n_embedding, struct mio_tts_params params,
+                                     float ** audio_out, size_t * n_audio_out, int32_t * sample_rate_out, char * err,
+                                     size_t err_size);
+
+/* lib.h:131-144, lib.cpp:1325-1366 */
+MIO_B200_API bool mio_tts_reserve_workspace(struct mio_tts_context * ctx, int32_t n_codes, char * err, size_t err_size);
+MIO_B200_API bool mio_tts_estimate_workspace_bytes(struct mio_tts_context * ctx, int32_t n_codes, uint64_t * out_bytes,
+                                                   char * err, size_t err_size);
+/* lib.h:147-160, lib.cpp:1368-1432 */
+MIO_B200_API bool mio_tts_reserve_reference_workspace(struct mio_tts_context * ctx, float max_reference_seconds,
+                                                      char * err, size_t err_size);
+MIO_B200_API bool mio_tts_estimate_reference_workspace_bytes(struct mio_tts_context * ctx, float max_reference_seconds,
+                                                             uint64_t * out_bytes, char * err, size_t err_size);
+
+/* lib.h:162-170, lib.cpp:758-791, 1434-1457 */
+MIO_B200_API bool mio_tts_audio_save_wav16(const char * path, const float * audio, size_t n_audio, int32_t sample_rate,
+                                           char * err, size_t err_size);
+MIO_B200_API void mio_tts_audio_free(float * audio);
+
+/* ------------------------------------------------------------------------------------------------
+ * Extensions (no reference counterpart)
+ * ------------------------------------------------------------------------------------------------ */
+
+/* Batched mio_tts_synthesize: `batch` utterances of arbitrary lengths decoded in one pass.
+ * codes[i] / n_codes[i] / embedding[i] (each n_embedding floats; NULL array for static models).
+ * audio_out[i] / n_audio_out[i] are filled per utterance; free each with mio_tts_audio_free. */
+MIO_B200_API bool mio_tts_b200_synthesize_batch(struct mio_tts_context * ctx, const int32_t * const * codes,
+                                                const size_t * n_codes, const float * const * embedding,
+                                                size_t n_embedding, size_t batch, struct mio_tts_params params,
+                                                float ** audio_out, size_t * n_audio_out, int32_t * sample_rate_out,
+                                                char * err, size_t err_size);
+
+/* Stage hooks for parity tests.  decode_spec mirrors miocodec_decoder::decode_tokens
+ * (/root/reference/src/miocodec-decoder.cpp:1079): spec_out = malloc'd [n_frames][n_bins]. */
+MIO_B200_API bool mio_tts_b200_decode_spec(struct mio_tts_context * ctx, const int32_t * codes, size_t n_codes,
+                                           const float * embedding, size_t n_embedding, float ** spec_out,
+                                           int32_t * n_frames_out, int32_t * n_bins_out, char * err, size_t err_size);
+/* ggml_get_rows(token_embd, codes) (miocodec-decoder.cpp:1360): out = caller buffer [n_codes][prenet_dim] */
+MIO_B200_API bool mio_tts_b200_gather(struct mio_tts_context * ctx, const int32_t * codes, size_t n_codes, float * out,
+                                      char * err, size_t err_size);
+/* Intermediate activations of utterance 0 after stage 1 prenet (:1365), 2 upsample+interpolate (:1374), 3 prior
+ * ResNets (:1380), 4 decoder + final AdaLN (:1400), 5 post ResNets (:1408): malloc'd fp32 [rows][cols]. */
+MIO_B200_API bool mio_tts_b200_debug_stage(struct mio_tts_context * ctx, const int32_t * codes, size_t n_codes,
+                                           const float * embedding, size_t n_embedding, int32_t stage, float ** out,
+                                           int32_t * rows_out, int32_t * cols_out, char * err, size_t err_size);
+MIO_B200_API int32_t mio_tts_b200_prenet_dim(const struct mio_tts_context * ctx);
+/* embd_to_audio (lib.cpp:625-756): spec [n_frames][n_fft+2] host -> malloc'd audio */
+MIO_B200_API bool mio_tts_b200_istft(struct mio_tts_context * ctx, const float * spec, int32_t n_frames, int32_t n_fft,
+                                     int32_t hop, float ** audio_out, size_t * n_audio_out, char * err, size_t err_size);
+MIO_B200_API void mio_tts_b200_free(void * p);   /* frees spec_out / istft audio_out (plain malloc) */
+/* 1 = use the generic SIMT attention kernel instead of the tensor-core band kernel (cross-check) */
+MIO_B200_API void mio_tts_b200_set_generic_attention(struct mio_tts_context * ctx, int32_t enable);
+
+/* Timing hooks for bench.py.  prepare uploads one batch into HBM; run_resident executes the device path
+ * `iters` times over the resident batch and returns the mean milliseconds per pass measured with CUDA events
+ * on the library's stream (<0 on error); profile fills stage/GEMM timings of one profiled pass. */
+struct mio_tts_b200_profile {
+    float prenet_ms, upsample_prior_ms, decoder_ms, post_head_ms, istft_ms, total_ms;
+    double gemm_ms, gemm_flops; int32_t gemm_launches;
+    double attn_ms; int32_t attn_launches;
+};
+MIO_B200_API bool mio_tts_b200_prepare(struct mio_tts_context * ctx, const int32_t * const * codes,
+                                       const size_t * n_codes, const float * const * embedding, size_t n_embedding,
+                                       size_t batch, char * err, size_t err_size);
+MIO_B200_API float mio_tts_b200_run_resident(struct mio_tts_context * ctx, int32_t iters, char * err, size_t err_size);
+MIO_B200_API bool mio_tts_b200_profile_resident(struct mio_tts_context * ctx, struct mio_tts_b200_profile * out,
+                                                char * err, size_t err_size);
+/* total audio samples of the prepared batch */
+MIO_B200_API uint64_t mio_tts_b200_resident_samples(struct mio_tts_context * ctx);
+/* iSTFT microbench (BASELINE config 3): synthetic spectra generated in HBM; returns ms per pass (<0 on error) */
+MIO_B200_API float mio_tts_b200_istft_bench(struct mio_tts_context * ctx, int32_t n_utt, int32_t frames_per_utt,
+                                            int32_t n_fft, int32_t hop, int32_t iters, uint64_t seed, double * checksum,
+                                            char * err, size_t err_size);
+/* number of this library's kernels launched so far in this process */
+MIO_B200_API uint64_t mio_tts_b200_launch_count(void);
+MIO_B200_API uint64_t mio_tts_b200_workspace_bytes(struct mio_tts_context * ctx);
+MIO_B200_API uint64_t mio_tts_b200_weight_bytes(struct mio_tts_context * ctx);
+/* bytes of the last batch's host->device upload (codes + embeddings + row tables) */
+MIO_B200_API uint64_t mio_tts_b200_last_h2d_bytes(struct mio_tts_context * ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MIO_TTS_B200_H */

@@ -1,0 +1,261 @@
+// Banded (local-window) multi-head attention for the MioCodec transformer blocks.
+//
+// Reference: softmax(Q K^T / sqrt(hd) + mask) V with mask 0 iff |q - k| <= window/2 else -inf, materialised as a
+// dense N x N matrix (/root/reference/src/miocodec-decoder.cpp:1251-1257, mask fill :1501-1525).  Here only the
+// band is computed: a CTA owns one 64-query tile of one head of one utterance and the <=128 keys it can see;
+// QK^T and PV run on tensor cores (mma.sync m16n8k16, fp32 accumulate) with the softmax in registers
+// (S accumulator fragments are re-used as the A operand of PV).  RoPE and the 1/sqrt(hd) scale were already
+// applied to q/k by the QKV GEMM epilogue.  A generic SIMT kernel covers other head sizes / wider windows.
+#include "common.h"
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+namespace mio {
+namespace {
+
+constexpr int TQ = 64;        // queries per tile
+constexpr int TK = 128;       // keys visible to a tile (TQ + 2*32)
+constexpr int HD = 64;        // head dim of the fast path
+constexpr int LDS = 72;       // padded smem row (elements): 144 B keeps ldmatrix / fragment loads conflict-free
+
+template <bool BF16>
+__device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    if constexpr (BF16) {
+        asm volatile(
+            "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+            : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+            : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+    } else {
+        asm volatile(
+            "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+            : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+            : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+    }
+}
+
+template <bool BF16> __device__ __forceinline__ uint32_t pack2(float a, float b) {
+    if constexpr (BF16) {
+        __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+        return *reinterpret_cast<uint32_t *>(&v);
+    } else {
+        __half2 v = __floats2half2_rn(a, b);
+        return *reinterpret_cast<uint32_t *>(&v);
+    }
+}
+
+template <bool BF16>
+__global__ void __launch_bounds__(128) attention_band_kernel(const uint16_t * __restrict__ qkv,
+                                                             uint16_t * __restrict__ out, int dim, int half_window,
+                                                             const row_tile * __restrict__ tiles) {
+    __shared__ __align__(16) uint16_t Qs[TQ * LDS];
+    __shared__ __align__(16) uint16_t Ks[TK * LDS];
+    __shared__ __align__(16) uint16_t Vs[TK * LDS];
+
+    const row_tile t = tiles[blockIdx.x];
+    const int head = blockIdx.y;
+    const int ld = 3 * dim;
+    const int kpos0 = t.pos0 - 32;     // position of key index 0
+
+    // ---- stage Q, K, V tiles (16-byte chunks; rows outside the utterance are zero) ----
+    for (int c = threadIdx.x; c < TQ * 8; c += blockDim.x) {
+        const int i = c >> 3, ch = c & 7;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (i < t.n) v = *reinterpret_cast<const uint4 *>(qkv + (size_t) (t.row0 + i) * ld + head * HD + ch * 8);
+        *reinterpret_cast<uint4 *>(Qs + i * LDS + ch * 8) = v;
+    }
+    for (int c = threadIdx.x; c < TK * 8; c += blockDim.x) {
+        const int j = c >> 3, ch = c & 7;
+        const int pos = kpos0 + j;
+        uint4 kv = make_uint4(0, 0, 0, 0), vv = make_uint4(0, 0, 0, 0);
+        if (pos >= 0 && pos < t.utt_len) {
+            const uint16_t * p = qkv + (size_t) (t.utt_row0 + pos) * ld + head * HD + ch * 8;
+            kv = *reinterpret_cast<const uint4 *>(p + dim);
+            vv = *reinterpret_cast<const uint4 *>(p + 2 * dim);
+        }
+        *reinterpret_cast<uint4 *>(Ks + j * LDS + ch * 8) = kv;
+        *reinterpret_cast<uint4 *>(Vs + j * LDS + ch * 8) = vv;
+    }
+    __syncthreads();
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = lane >> 2, tq = lane & 3;
+    const int q0 = warp * 16;          // first query of this warp; its keys are indices [q0, q0 + 80)
+
+    // ---- S = Q K^T (16 x 80) ----
+    uint32_t qa[4][4];
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk) {
+        const uint16_t * base = Qs + (q0 + g) * LDS + kk * 16 + 2 * tq;
+        qa[kk][0] = *reinterpret_cast<const uint32_t *>(base);
+        qa[kk][1] = *reinterpret_cast<const uint32_t *>(base + 8 * LDS);
+        qa[kk][2] = *reinterpret_cast<const uint32_t *>(base + 8);
+        qa[kk][3] = *reinterpret_cast<const uint32_t *>(base + 8 * LDS + 8);
+    }
+    float s[10][4];
+#pragma unroll
+    for (int nt = 0; nt < 10; ++nt) {
+        s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.0f;
+        const uint16_t * kb = Ks + (q0 + nt * 8 + g) * LDS + 2 * tq;
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+            const uint32_t b0 = *reinterpret_cast<const uint32_t *>(kb + kk * 16);
+            const uint32_t b1 = *reinterpret_cast<const uint32_t *>(kb + kk * 16 + 8);
+            mma16816<BF16>(s[nt], qa[kk], b0, b1);
+        }
+    }
+
+    // ---- band mask + softmax (rows g and g+8 of this warp's 16 queries) ----
+    const int qi0 = q0 + g, qi1 = q0 + g + 8;             // query index in tile
+    const int qp0 = t.pos0 + qi0, qp1 = t.pos0 + qi1;     // positions
+    const bool qv0 = qi0 < t.n, qv1 = qi1 < t.n;
+    float m0 = -INFINITY, m1 = -INFINITY;
+#pragma unroll
+    for (int nt = 0; nt < 10; ++nt) {
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const int kp = kpos0 + q0 + nt * 8 + 2 * tq + e;
+            const bool kvld = kp >= 0 && kp < t.utt_len;
+            const bool ok0 = qv0 && kvld && abs(kp - qp0) <= half_window;
+            const bool ok1 = qv1 && kvld && abs(kp - qp1) <= half_window;
+            s[nt][e] = ok0 ? s[nt][e] : -INFINITY;
+            s[nt][2 + e] = ok1 ? s[nt][2 + e] : -INFINITY;
+            m0 = fmaxf(m0, s[nt][e]);
+            m1 = fmaxf(m1, s[nt][2 + e]);
+        }
+    }
+    m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1));
+    m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
+    m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 1));
+    m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 2));
+    if (m0 == -INFINITY) m0 = 0.0f;
+    if (m1 == -INFINITY) m1 = 0.0f;
+    float l0 = 0.0f, l1 = 0.0f;
+#pragma unroll
+    for (int nt = 0; nt < 10; ++nt) {
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            s[nt][e] = __expf(s[nt][e] - m0);
+            s[nt][2 + e] = __expf(s[nt][2 + e] - m1);
+            l0 += s[nt][e];
+            l1 += s[nt][2 + e];
+        }
+    }
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+
+    // ---- O = P V (16 x 64), P fragments straight from the S accumulators ----
+    float o[8][4];
+#pragma unroll
+    for (int nd = 0; nd < 8; ++nd) o[nd][0] = o[nd][1] = o[nd][2] = o[nd][3] = 0.0f;
+#pragma unroll
+    for (int kk = 0; kk < 5; ++kk) {
+        uint32_t pa[4];
+        pa[0] = pack2<BF16>(s[2 * kk][0], s[2 * kk][1]);
+        pa[1] = pack2<BF16>(s[2 * kk][2], s[2 * kk][3]);
+        pa[2] = pack2<BF16>(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+        pa[3] = pack2<BF16>(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+        const int mi = lane >> 3, mr = lane & 7;
+        const int key = q0 + kk * 16 + (mi & 1) * 8 + mr;
+#pragma unroll
+        for (int nd = 0; nd < 8; nd += 2) {
+            const uint32_t addr = (uint32_t) __cvta_generic_to_shared(Vs + key * LDS + (nd + (mi >> 1)) * 8);
+            uint32_t b0, b1, b2, b3;
+            asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(b0), "=r"(b1), "=r"(b2), "=r"(b3)
+                         : "r"(addr));
+            mma16816<BF16>(o[nd], pa, b0, b1);
+            mma16816<BF16>(o[nd + 1], pa, b2, b3);
+        }
+    }
+
+    const float inv0 = l0 > 0.0f ? 1.0f / l0 : 0.0f;
+    const float inv1 = l1 > 0.0f ? 1.0f / l1 : 0.0f;
+#pragma unroll
+    for (int nd = 0; nd < 8; ++nd) {
+        const int col = head * HD + nd * 8 + 2 * tq;
+        if (qv0)
+            *reinterpret_cast<uint32_t *>(out + (size_t) (t.row0 + qi0) * dim + col) =
+                pack2<BF16>(o[nd][0] * inv0, o[nd][1] * inv0);
+        if (qv1)
+            *reinterpret_cast<uint32_t *>(out + (size_t) (t.row0 + qi1) * dim + col) =
+                pack2<BF16>(o[nd][2] * inv1, o[nd][3] * inv1);
+    }
+}
+
+// ---- generic fallback: one warp per (query, head); any head_dim, any window ----
+template <bool BF16> __device__ __forceinline__ float ld16(const uint16_t * p) {
+    if constexpr (BF16) return __bfloat162float(*reinterpret_cast<const __nv_bfloat16 *>(p));
+    else return __half2float(*reinterpret_cast<const __half *>(p));
+}
+template <bool BF16> __device__ __forceinline__ uint16_t st16(float v) {
+    if constexpr (BF16) { __nv_bfloat16 h = __float2bfloat16_rn(v); return *reinterpret_cast<uint16_t *>(&h); }
+    else { __half h = __float2half_rn(v); return *reinterpret_cast<uint16_t *>(&h); }
+}
+
+template <bool BF16>
+__global__ void attention_generic_kernel(const uint16_t * __restrict__ qkv, uint16_t * __restrict__ out, int dim,
+                                         int head_dim, int half_window, const row_tile * __restrict__ tiles) {
+    extern __shared__ float sc[];   // [warps][2*half_window+1]
+    const row_tile t = tiles[blockIdx.x];
+    const int head = blockIdx.y;
+    const int warps = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int ld = 3 * dim;
+    float * my = sc + (size_t) warp * (2 * half_window + 1);
+    for (int i = warp; i < t.n; i += warps) {
+        const int qp = t.pos0 + i;
+        const int k_lo = max(0, qp - half_window), k_hi = min(t.utt_len - 1, qp + half_window);
+        const int nk = k_hi - k_lo + 1;
+        const uint16_t * q = qkv + (size_t) (t.row0 + i) * ld + head * head_dim;
+        float mx = -INFINITY;
+        for (int j = lane; j < nk; j += 32) {
+            const uint16_t * k = qkv + (size_t) (t.utt_row0 + k_lo + j) * ld + dim + head * head_dim;
+            float acc = 0.0f;
+            for (int d = 0; d < head_dim; ++d) acc += ld16<BF16>(q + d) * ld16<BF16>(k + d);
+            my[j] = acc;
+            mx = fmaxf(mx, acc);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        float sum = 0.0f;
+        for (int j = lane; j < nk; j += 32) { const float p = __expf(my[j] - mx); my[j] = p; sum += p; }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        __syncwarp();
+        const float inv = 1.0f / sum;
+        for (int d = lane; d < head_dim; d += 32) {
+            float acc = 0.0f;
+            for (int j = 0; j < nk; ++j)
+                acc += my[j] * ld16<BF16>(qkv + (size_t) (t.utt_row0 + k_lo + j) * ld + 2 * dim + head * head_dim + d);
+            out[(size_t) (t.row0 + i) * dim + head * head_dim + d] = st16<BF16>(acc * inv);
+        }
+        __syncwarp();
+    }
+}
+
+} // namespace
+
+void launch_attention(const void * qkv16, void * out16, int dtype, int dim, int heads, int window,
+                      const row_tile * tiles, int n_tiles, bool force_generic, cudaStream_t st) {
+    if (n_tiles <= 0) return;
+    const int head_dim = dim / heads;
+    const int half = window / 2;
+    dim3 grid((unsigned) n_tiles, (unsigned) heads);
+    const uint16_t * q = (const uint16_t *) qkv16;
+    uint16_t * o = (uint16_t *) out16;
+    if (!force_generic && head_dim == HD && half <= 32 && (dim % 8) == 0) {
+        if (dtype == OP_BF16) attention_band_kernel<true><<<grid, 128, 0, st>>>(q, o, dim, half, tiles);
+        else attention_band_kernel<false><<<grid, 128, 0, st>>>(q, o, dim, half, tiles);
+    } else {
+        const size_t smem = 4 * (size_t) (2 * half + 1) * sizeof(float);
+        if (smem > 48 * 1024) throw cuda_error("attention: window too large for the generic kernel");
+        if (dtype == OP_BF16) attention_generic_kernel<true><<<grid, 128, smem, st>>>(q, o, dim, head_dim, half, tiles);
+        else attention_generic_kernel<false><<<grid, 128, smem, st>>>(q, o, dim, head_dim, half, tiles);
+    }
+    MIO_CUDA(cudaGetLastError());
+    count_launch();
+}
+
+} // namespace mio

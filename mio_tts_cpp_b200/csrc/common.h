@@ -1,0 +1,135 @@
+// Shared host/device declarations for the B200 MioCodec decode + iSTFT path.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda.h>
+#include <atomic>
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+
+namespace mio {
+
+struct cuda_error : std::runtime_error {
+    explicit cuda_error(const std::string & m) : std::runtime_error(m) {}
+};
+
+inline void cuda_check(cudaError_t e, const char * what, const char * file, int line) {
+    if (e != cudaSuccess) {
+        throw cuda_error(std::string("CUDA error: ") + cudaGetErrorString(e) + " (" + what + ") at " + file + ":" +
+                         std::to_string(line));
+    }
+}
+#define MIO_CUDA(x) ::mio::cuda_check((x), #x, __FILE__, __LINE__)
+
+// every launch of one of OUR kernels bumps this (bench.py reports it as gpu_launches)
+extern std::atomic<unsigned long long> g_launch_count;
+inline void count_launch(int n = 1) { g_launch_count.fetch_add((unsigned long long) n, std::memory_order_relaxed); }
+
+// 16-bit operand formats of the tensor-core GEMMs (tcgen05 kind::f16 a/b_format field)
+enum op16 : int { OP_F16 = 0, OP_BF16 = 1 };
+
+// ---------------------------------------------------------------------------------------------
+// Row layouts.  Activations are [rows, channels] row-major (channel-contiguous).  A layout packs
+// the utterances of a batch along rows; `gap` zero rows separate utterances (and precede the
+// first / follow the last) so a k=3 convolution can read row+-1 without per-utterance branches.
+// ---------------------------------------------------------------------------------------------
+struct row_tile {        // a run of <= 64 rows inside ONE utterance (attention / statistics work unit)
+    int row0;            // first row (layout coordinates)
+    int n;               // rows in this tile
+    int utt;             // utterance index
+    int pos0;            // position of row0 inside the utterance
+    int utt_row0;        // first row of the utterance
+    int utt_len;         // rows of the utterance
+};
+
+// ---------------------------------------------------------------------------------------------
+// GEMM (gemm_tcgen05.cu):  D[M,N] = A[M, taps*K] * W[N, taps*K]^T with fused epilogues
+// ---------------------------------------------------------------------------------------------
+enum gemm_epilogue : int {
+    EPI_STORE32 = 0,   // out32[r,n] = (acc + bias[n]) * gate[utt(r),n] + res[r,n]   (each term optional)
+    EPI_STORE16 = 1,   // out16[r,n] = acc + bias[n]
+    EPI_SWIGLU16 = 2,  // out16[r,n/2] = silu(acc[r,2j]) * acc[r,2j+1]   (weights interleaved gate/up)
+    EPI_ROPE16 = 3,    // out16[r,n] = rope(acc) for n < rope_cols (q,k), q scaled; plain for v
+};
+
+struct gemm_args {
+    CUtensorMap map_a;       // A: [rows, K] 16-bit, box 64 x 128, swizzle 128B
+    CUtensorMap map_b;       // W: [N, taps*K] 16-bit, box 64 x BLOCK_N, swizzle 128B
+    int M, N, K, taps;
+    int dtype;               // op16 of A and W
+    int out_dtype;           // op16 of a 16-bit output
+    int epilogue;
+    void * out; int ldo;
+    const float * bias;
+    const float * res; int ldr;
+    const float * gate; int gate_ld;     // gate[utt * gate_ld + n]
+    const int * row_utt;                 // row -> utterance (needed with gate)
+    const int * row_pos;                 // row -> position in utterance (needed with rope)
+    const float2 * rope;                 // [pos, head_dim/2] (cos, sin)
+    int rope_cols, head_dim, q_cols; float q_scale;
+};
+
+void gemm_launch(const gemm_args & a, int num_sms, cudaStream_t st);
+// A-operand / weight tensor maps (row-major [rows, cols] 16-bit, cols contiguous)
+CUtensorMap make_tmap_16(const void * ptr, uint64_t rows, uint64_t cols, uint32_t box_rows);
+int gemm_block_n(int N);   // tile width the launcher will use for this N (weights' map box must match)
+
+// ---------------------------------------------------------------------------------------------
+// elementwise / normalisation kernels (ops.cu)
+// ---------------------------------------------------------------------------------------------
+void launch_gather(const float * table, const int * codes, float * out, int n_rows, int dim, cudaStream_t st);
+void launch_cond(const float * w, const float * b, const float * emb, float * out, int n_out, int adim, int n_utt,
+                 cudaStream_t st);
+// LayerNorm over channels; affine (w,b) or AdaLN (shift,scale per utterance at cond + utt*cond_ld + off)
+void launch_layernorm(const float * x, int rows, int dim, float eps, const float * w, const float * b,
+                      const float * cond, int cond_ld, int shift_off, int scale_off, const int * row_utt,
+                      void * out16, int out_dtype, float * out32, cudaStream_t st);
+void launch_cast16(const float * x, void * out16, int out_dtype, size_t n, cudaStream_t st);
+void launch_gn_stats(const float * x, int dim, int groups, const row_tile * tiles, int n_tiles, double * stats,
+                     cudaStream_t st);
+// (sum, sumsq) -> (mean, rstd) per (utterance, group)
+void launch_gn_finalize(const double * stats, const int * utt_len, int cpg, int groups, int n_utt, float eps,
+                        float2 * mean_rstd, cudaStream_t st);
+// normalise + affine + SiLU -> 16-bit conv operand; gap rows of the layout are written as zeros
+void launch_gn_apply(const float * x, int rows, int dim, int groups, const float2 * mean_rstd, const float * w,
+                     const float * b, const int * row_utt, void * out16, int out_dtype, cudaStream_t st);
+// ggml_interpolate(bilinear, width only) from the x2 transposed-conv output to the decoder frame layout
+void launch_interp(const float * src, const int * src_row0, const int * src_len, float * dst, int rows, int dim,
+                   const int * row_utt, const int * row_pos, const int * utt_len, cudaStream_t st);
+void launch_rope_table(float2 * table, int n_pos, int half_dim, float theta_scale, cudaStream_t st);
+// wave-upsampler: col2im of a transposed conv GEMM output + bias + crop + SnakeBeta
+void launch_convt_fold_snake(const float * y, int ld_y, const int * src_row0, const int * src_len, float * dst,
+                             int rows, int cout, int ksize, int stride, int pad, const float * bias,
+                             const float * snake_a, const float * snake_inv_b, const int * row_utt,
+                             const int * row_pos, cudaStream_t st);
+void launch_snake(float * x, int rows, int dim, const float * snake_a, const float * snake_inv_b, cudaStream_t st);
+
+// ---------------------------------------------------------------------------------------------
+// banded attention (attention.cu): qkv16 [rows, 3*dim] (RoPE + scale already applied) -> out16 [rows, dim]
+// ---------------------------------------------------------------------------------------------
+void launch_attention(const void * qkv16, void * out16, int dtype, int dim, int heads, int window,
+                      const row_tile * tiles, int n_tiles, bool force_generic, cudaStream_t st);
+
+// ---------------------------------------------------------------------------------------------
+// iSTFT (istft.cu)
+// ---------------------------------------------------------------------------------------------
+struct istft_plan {
+    int n_fft = 0, hop = 0;
+    int n_radix = 0;
+    int radix[16] = {0};
+    float2 * d_tw_m = nullptr;    // exp(+2 pi i j / M), j < M = n_fft/2
+    float2 * d_tw_n = nullptr;    // exp(+2 pi i k / n_fft), k <= M/2
+    float * d_hann = nullptr;     // periodic Hann, host cosf (src/mio-tts-lib.cpp:415-420)
+    size_t smem_bytes = 0;
+};
+bool istft_plan_init(istft_plan & p, int n_fft, int hop, std::string & err);
+void istft_plan_free(istft_plan & p);
+// spec: rows in a layout (utterance u: rows spec_row0[u] .. +n_frames[u]), pitch floats per row.
+// audio: utterance u at audio + audio_off[u], n_frames[u]*hop samples (when n_fft-hop is even).
+void launch_istft(const istft_plan & p, const float * spec, int pitch, const int * spec_row0, const int * n_frames,
+                  const long long * audio_off, float * audio, unsigned int * peak_bits, int n_utt, int max_frames,
+                  cudaStream_t st);
+void launch_peak_normalize(float * audio, const long long * audio_off, const long long * audio_len,
+                           const unsigned int * peak_bits, int n_utt, long long max_len, cudaStream_t st);
+
+} // namespace mio

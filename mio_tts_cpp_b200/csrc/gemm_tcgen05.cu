@@ -1,0 +1,433 @@
+// tcgen05 / TMEM / TMA GEMM for the MioCodec decoder's dense contractions (sm_100a only).
+//
+//   D[M, N] = sum_{tap < taps} A[row + tap - taps/2, 0:K] * W[N, tap*K : (tap+1)*K]^T      (fp32 accumulate)
+//
+// taps = 1: the linears of transformer_block_eval / linear()  (/root/reference/src/miocodec-decoder.cpp:128-134,
+//           1190-1291), the x2 transposed conv as one [.,2*C] GEMM (:1368-1372) and the iSTFT head (:1460).
+// taps = 3: ggml_conv_1d_ph k=3 of resnet_block_eval (:1293-1330) as an implicit GEMM: three row-shifted TMA
+//           loads of the same [rows, C] activation; zero gap rows of the row layout give the "same" padding.
+//
+// Structure (one persistent CTA per SM, 192 threads):
+//   warp 0      TMA producer: cp.async.bulk.tensor.2d -> 128B-swizzled smem stages, mbarrier complete_tx
+//   warp 1      allocates TMEM; one lane issues tcgen05.mma.cta_group::1.kind::f16 (M=128, N=BLOCK_N, K=16),
+//               tcgen05.commit releases smem stages / publishes the accumulator
+//   warps 2..5  epilogue: tcgen05.ld 32x32b.x32 -> registers -> fused bias / gate / residual / SwiGLU / RoPE
+//               -> vectorised global stores.  Two TMEM accumulator buffers overlap epilogue(i) with MMA(i+1).
+#include "common.h"
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include <atomic>
+#include <mutex>
+
+namespace mio {
+
+std::atomic<unsigned long long> g_launch_count{0};
+
+namespace {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;      // 16-bit elements -> 128-byte rows = one SWIZZLE_128B atom
+constexpr int UMMA_K = 16;
+constexpr int GEMM_THREADS = 192;
+
+template <int BN> struct tile_cfg {
+    static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
+    static constexpr int B_BYTES = BN * BLOCK_K * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES = BN == 256 ? 4 : 6;
+    static constexpr int TMEM_COLS = 2 * BN;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    long long t0 = 0;
+    while (true) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (done) break;
+        // a protocol bug must not hang the GPU: trap after ~2 s of waiting
+        if (t0 == 0) t0 = clock64();
+        else if (clock64() - t0 > 4000000000ll) __trap();
+    }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap * map, uint32_t bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"((uint64_t) map), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tcgen05_mma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                                uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout):
+// start>>4 [0,14) | LBO>>4 [16,30) | SBO>>4 [32,46) | version=1 [46,48) | layout SWIZZLE_128B=2 [61,64)
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= (uint64_t) ((smem_addr >> 4) & 0x3FFF);
+    d |= (uint64_t) 1 << 16;                 // leading byte offset (unused for swizzled K-major), 16 B
+    d |= (uint64_t) (1024 >> 4) << 32;       // stride byte offset: 8 rows x 128 B
+    d |= (uint64_t) 1 << 46;                 // descriptor version (Blackwell)
+    d |= (uint64_t) 2 << 61;                 // SWIZZLE_128B
+    return d;
+}
+
+__device__ __forceinline__ uint32_t pack16(float a, float b, int dtype) {
+    if (dtype == OP_BF16) {
+        __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+        return *reinterpret_cast<uint32_t *>(&v);
+    }
+    __half2 v = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t *>(&v);
+}
+
+__device__ __forceinline__ float silu_f(float x) { return x / (1.0f + __expf(-x)); }
+
+// ---- epilogue of one 32-column chunk held by one thread (row r, columns n .. n+31) ----------------
+template <int EPI>
+__device__ __forceinline__ void epilogue_chunk(const gemm_args & a, int r, int n, uint32_t (&raw)[32]) {
+    float v[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]);
+    const bool full = n + 32 <= a.N;
+
+    if constexpr (EPI == EPI_STORE32) {
+        float * orow = (float *) a.out + (size_t) r * a.ldo + n;
+        const float * gate = a.gate ? a.gate + (size_t) max(a.row_utt[r], 0) * a.gate_ld + n : nullptr;
+        const float * res = a.res ? a.res + (size_t) r * a.ldr + n : nullptr;
+        const bool vec = full && (a.ldo & 3) == 0 && (!res || (a.ldr & 3) == 0);
+        if (vec) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+                float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                if (a.bias) {
+                    const float4 b = __ldg(reinterpret_cast<const float4 *>(a.bias + n + j));
+                    o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
+                }
+                if (gate) {
+                    const float4 g = __ldg(reinterpret_cast<const float4 *>(gate + j));
+                    o.x *= g.x; o.y *= g.y; o.z *= g.z; o.w *= g.w;
+                }
+                if (res) {
+                    const float4 q = *reinterpret_cast<const float4 *>(res + j);
+                    o.x += q.x; o.y += q.y; o.z += q.z; o.w += q.w;
+                }
+                *reinterpret_cast<float4 *>(orow + j) = o;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                if (n + j < a.N) {
+                    float o = v[j];
+                    if (a.bias) o += a.bias[n + j];
+                    if (gate) o *= gate[j];
+                    if (res) o += res[j];
+                    orow[j] = o;
+                }
+            }
+        }
+    } else if constexpr (EPI == EPI_STORE16 || EPI == EPI_ROPE16) {
+        if (a.bias) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) if (n + j < a.N) v[j] += a.bias[n + j];
+        }
+        if constexpr (EPI == EPI_ROPE16) {
+            if (n < a.rope_cols) {   // q and k columns; a 32-column chunk never straddles a head (head_dim % 32 == 0)
+                const int half = a.head_dim >> 1;
+                const float2 * cs = a.rope + (size_t) a.row_pos[r] * half + ((n % a.head_dim) >> 1);
+                const float s = n < a.q_cols ? a.q_scale : 1.0f;
+#pragma unroll
+                for (int i = 0; i < 16; i += 2) {
+                    const float4 c2 = __ldg(reinterpret_cast<const float4 *>(cs + i));   // (cos,sin) x 2
+                    const float x0 = v[2 * i], x1 = v[2 * i + 1], y0 = v[2 * i + 2], y1 = v[2 * i + 3];
+                    v[2 * i]     = (x0 * c2.x - x1 * c2.y) * s;
+                    v[2 * i + 1] = (x0 * c2.y + x1 * c2.x) * s;
+                    v[2 * i + 2] = (y0 * c2.z - y1 * c2.w) * s;
+                    v[2 * i + 3] = (y0 * c2.w + y1 * c2.z) * s;
+                }
+            }
+        }
+        if (full && (a.ldo & 7) == 0) {
+            uint4 * orow = reinterpret_cast<uint4 *>((uint16_t *) a.out + (size_t) r * a.ldo + n);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                uint4 o;
+                o.x = pack16(v[8 * j + 0], v[8 * j + 1], a.out_dtype);
+                o.y = pack16(v[8 * j + 2], v[8 * j + 3], a.out_dtype);
+                o.z = pack16(v[8 * j + 4], v[8 * j + 5], a.out_dtype);
+                o.w = pack16(v[8 * j + 6], v[8 * j + 7], a.out_dtype);
+                orow[j] = o;
+            }
+        } else {
+            uint16_t * orow = (uint16_t *) a.out + (size_t) r * a.ldo + n;
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (n + j < a.N) orow[j] = (uint16_t) (pack16(v[j], 0.0f, a.out_dtype) & 0xFFFF);
+        }
+    } else {   // EPI_SWIGLU16: columns (2j, 2j+1) = (gate_j, up_j)
+        const int no = n >> 1;
+        float h[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) h[j] = silu_f(v[2 * j]) * v[2 * j + 1];
+        if (full && (a.ldo & 7) == 0) {
+            uint4 * orow = reinterpret_cast<uint4 *>((uint16_t *) a.out + (size_t) r * a.ldo + no);
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                uint4 o;
+                o.x = pack16(h[8 * j + 0], h[8 * j + 1], a.out_dtype);
+                o.y = pack16(h[8 * j + 2], h[8 * j + 3], a.out_dtype);
+                o.z = pack16(h[8 * j + 4], h[8 * j + 5], a.out_dtype);
+                o.w = pack16(h[8 * j + 6], h[8 * j + 7], a.out_dtype);
+                orow[j] = o;
+            }
+        } else {
+            uint16_t * orow = (uint16_t *) a.out + (size_t) r * a.ldo + no;
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+                if (n + 2 * j + 1 < a.N) orow[j] = (uint16_t) (pack16(h[j], 0.0f, a.out_dtype) & 0xFFFF);
+        }
+    }
+}
+
+template <int BN, int EPI>
+__global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tcgen05_kernel(const __grid_constant__ gemm_args a) {
+    using C = tile_cfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_base = smem_base + C::STAGES * C::STAGE_BYTES;
+    // barriers: full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2]; then the TMEM base address
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (C::STAGES + s); };
+    auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * C::STAGES + s); };
+    auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * C::STAGES + 2 + s); };
+    const uint32_t tmem_slot = bar_base + 8u * (2 * C::STAGES + 4);
+    volatile uint32_t * tmem_slot_ptr =
+        reinterpret_cast<volatile uint32_t *>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    const int num_m_tiles = (a.M + BLOCK_M - 1) / BLOCK_M;
+    const int num_n_tiles = (a.N + BN - 1) / BN;
+    const int num_tiles = num_m_tiles * num_n_tiles;
+    const int k_blocks = (a.K + BLOCK_K - 1) / BLOCK_K;
+    const int k_iters = k_blocks * a.taps;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < C::STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot),
+                     "r"((uint32_t) C::TMEM_COLS)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            uint32_t kit = 0;
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+                const int m0 = (t / num_n_tiles) * BLOCK_M;
+                const int n0 = (t % num_n_tiles) * BN;
+                for (int tap = 0; tap < a.taps; ++tap) {
+                    const int arow = m0 + tap - (a.taps >> 1);
+                    for (int kb = 0; kb < k_blocks; ++kb, ++kit) {
+                        const int s = kit % C::STAGES;
+                        mbar_wait(empty_bar(s), ((kit / C::STAGES) & 1) ^ 1);
+                        mbar_expect_tx(full_bar(s), C::STAGE_BYTES);
+                        const uint32_t sa = smem_base + s * C::STAGE_BYTES;
+                        tma_load_2d(sa, &a.map_a, full_bar(s), kb * BLOCK_K, arow);
+                        tma_load_2d(sa + C::A_BYTES, &a.map_b, full_bar(s), tap * a.K + kb * BLOCK_K, n0);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        if (lane == 0) {
+            // instruction descriptor (cute::UMMA::InstrDescriptor): c=f32 [4,6), a/b format [7,10)/[10,13),
+            // K-major a/b (bits 15,16 = 0), N>>3 [17,23), M>>4 [24,29)
+            const uint32_t idesc = (1u << 4) | ((uint32_t) a.dtype << 7) | ((uint32_t) a.dtype << 10) |
+                                   ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (BLOCK_M >> 4) << 24);
+            uint32_t kit = 0, it = 0;
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+                const int acc = it & 1;
+                mbar_wait(tempty_bar(acc), ((it >> 1) & 1) ^ 1);
+                tcgen05_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * BN;
+                for (int ki = 0; ki < k_iters; ++ki, ++kit) {
+                    const int s = kit % C::STAGES;
+                    mbar_wait(full_bar(s), (kit / C::STAGES) & 1);
+                    tcgen05_fence_after();
+                    const uint32_t sa = smem_base + s * C::STAGE_BYTES;
+                    const uint64_t da = umma_desc_sw128(sa);
+                    const uint64_t db = umma_desc_sw128(sa + C::A_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                        // advance 32 bytes (16 elements) inside the 128B swizzle atom: +2 in the >>4 address field
+                        tcgen05_mma_f16(tmem_d, da + 2 * k, db + 2 * k, idesc, (ki | k) != 0);
+                    }
+                    tcgen05_commit(empty_bar(s));   // frees the smem stage once these MMAs retire
+                }
+                tcgen05_commit(tfull_bar(acc));     // accumulator complete
+            }
+        }
+    } else {
+        // ===== epilogue warps =====
+        const int quad = warp & 3;                   // TMEM lane quadrant this warp may access
+        uint32_t it = 0;
+        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+            const int m0 = (t / num_n_tiles) * BLOCK_M;
+            const int n0 = (t % num_n_tiles) * BN;
+            const int acc = it & 1;
+            mbar_wait(tfull_bar(acc), (it >> 1) & 1);
+            tcgen05_fence_after();
+            const int r = m0 + quad * 32 + lane;
+            const uint32_t taddr = tmem_base + ((uint32_t) (quad * 32) << 16) + acc * BN;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                const int n = n0 + c * 32;
+                if (n >= a.N) break;                 // warp-uniform
+                uint32_t raw[32];
+                tmem_ld_32x32b_x32(taddr + c * 32, raw);
+                tmem_ld_wait();
+                if (r < a.M) epilogue_chunk<EPI>(a, r, n, raw);
+            }
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty_bar(acc));
+        }
+    }
+
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tcgen05_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                     "r"((uint32_t) C::TMEM_COLS)
+                     : "memory");
+    }
+}
+
+typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+encode_tiled_fn get_encode_fn() {
+    static encode_tiled_fn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void * p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess) {
+            fn = (encode_tiled_fn) p;
+        }
+    });
+    if (!fn) throw cuda_error("cuTensorMapEncodeTiled is not available from the CUDA driver");
+    return fn;
+}
+
+template <int BN, int EPI> void launch_t(const gemm_args & a, int num_sms, cudaStream_t st) {
+    using C = tile_cfg<BN>;
+    static bool configured[64] = {false};   // per-device function attribute
+    int dev = 0;
+    MIO_CUDA(cudaGetDevice(&dev));
+    if (!configured[dev & 63]) {
+        MIO_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      C::SMEM_BYTES));
+        configured[dev & 63] = true;
+    }
+    const int tiles = ((a.M + BLOCK_M - 1) / BLOCK_M) * ((a.N + BN - 1) / BN);
+    const int grid = tiles < num_sms ? tiles : num_sms;
+    gemm_tcgen05_kernel<BN, EPI><<<grid, GEMM_THREADS, C::SMEM_BYTES, st>>>(a);
+    MIO_CUDA(cudaGetLastError());
+    count_launch();
+}
+
+template <int BN> void launch_bn(const gemm_args & a, int num_sms, cudaStream_t st) {
+    switch (a.epilogue) {
+        case EPI_STORE32: launch_t<BN, EPI_STORE32>(a, num_sms, st); break;
+        case EPI_STORE16: launch_t<BN, EPI_STORE16>(a, num_sms, st); break;
+        case EPI_SWIGLU16: launch_t<BN, EPI_SWIGLU16>(a, num_sms, st); break;
+        case EPI_ROPE16: launch_t<BN, EPI_ROPE16>(a, num_sms, st); break;
+        default: throw cuda_error("gemm: bad epilogue");
+    }
+}
+
+} // namespace
+
+int gemm_block_n(int N) { return N >= 256 ? 256 : 128; }
+
+CUtensorMap make_tmap_16(const void * ptr, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+    if ((cols % 8) != 0) throw cuda_error("tensor map: row pitch must be a multiple of 16 bytes");
+    CUtensorMap m;
+    const cuuint64_t dims[2] = {cols, rows};
+    const cuuint64_t strides[1] = {cols * 2};
+    const cuuint32_t box[2] = {(cuuint32_t) BLOCK_K, box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = get_encode_fn()(&m, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, const_cast<void *>(ptr), dims, strides,
+                                       box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                       CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) throw cuda_error("cuTensorMapEncodeTiled failed: " + std::to_string((int) r));
+    return m;
+}
+
+void gemm_launch(const gemm_args & a, int num_sms, cudaStream_t st) {
+    if (a.M <= 0 || a.N <= 0 || a.K <= 0) return;
+    if (a.epilogue == EPI_ROPE16 && (a.head_dim % 32) != 0) throw cuda_error("gemm: rope epilogue needs head_dim % 32 == 0");
+    if (gemm_block_n(a.N) == 256) launch_bn<256>(a, num_sms, st);
+    else launch_bn<128>(a, num_sms, st);
+}
+
+} // namespace mio

@@ -1,0 +1,450 @@
+// Coalesced, vectorised warp-shuffle kernels for the HBM-bound pieces of the MioCodec decode path:
+// codebook gather, AdaLN conditioning vectors, LayerNorm(+affine / AdaLN), GroupNorm (two-phase) + SiLU,
+// bilinear frame interpolation, RoPE table, transposed-conv fold + SnakeBeta (wave-upsampler branch).
+// Reference semantics are cited per kernel (paths relative to /root/reference).
+#include "common.h"
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+namespace mio {
+namespace {
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__device__ __forceinline__ uint32_t pack16(float a, float b, int dtype) {
+    if (dtype == OP_BF16) {
+        __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+        return *reinterpret_cast<uint32_t *>(&v);
+    }
+    __half2 v = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t *>(&v);
+}
+
+__device__ __forceinline__ float silu_exact(float x) { return x / (1.0f + expf(-x)); }
+
+// ---- A1: ggml_get_rows(token_embd, codes), src/miocodec-decoder.cpp:1360.  Pure copy: bit-exact. ----------
+__global__ void gather_kernel(const float * __restrict__ table, const int * __restrict__ codes,
+                              float * __restrict__ out, int n_rows, int dim) {
+    const int warps_per_block = blockDim.x >> 5;
+    const int row = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
+    if (row >= n_rows) return;
+    const int lane = threadIdx.x & 31;
+    const float * src = table + (size_t) codes[row] * dim;
+    float * dst = out + (size_t) row * dim;
+    if ((dim & 3) == 0) {
+        const float4 * s4 = reinterpret_cast<const float4 *>(src);
+        float4 * d4 = reinterpret_cast<float4 *>(dst);
+        for (int i = lane; i < (dim >> 2); i += 32) d4[i] = __ldg(s4 + i);
+    } else {
+        for (int i = lane; i < dim; i += 32) dst[i] = __ldg(src + i);
+    }
+}
+
+// ---- AdaLN conditioning: p = W * silu(emb) + b for every conditioned norm at once
+//      (src/miocodec-decoder.cpp:1164-1181 cond = silu(embedding); :1204-1210, :1271-1277, :1390-1400) ----
+__global__ void cond_kernel(const float * __restrict__ w, const float * __restrict__ b,
+                            const float * __restrict__ emb, float * __restrict__ out, int n_out, int adim) {
+    const int utt = blockIdx.y;
+    const int j = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (j >= n_out) return;
+    const int lane = threadIdx.x & 31;
+    const float * e = emb + (size_t) utt * adim;
+    const float * wr = w + (size_t) j * adim;
+    float acc = 0.0f;
+    for (int i = lane; i < adim; i += 32) acc += __ldg(wr + i) * silu_exact(e[i]);
+    acc = warp_sum(acc);
+    if (lane == 0) out[(size_t) utt * n_out + j] = acc + b[j];
+}
+
+// ---- LayerNorm (ggml_norm, biased variance, ggml-cpu/ops.cpp:3642-3687) + affine (layer_norm(),
+//      src/miocodec-decoder.cpp:136-150) or AdaLN xn*(1+scale)+shift (adaln_apply :1183-1188).
+//      One warp per row, row kept in registers (dim = 128*NV), fp32 statistics, 16-bit or fp32 output. ----
+template <int NV>
+__global__ void layernorm_kernel(const float * __restrict__ x, int rows, float eps, const float * __restrict__ w,
+                                 const float * __restrict__ b, const float * __restrict__ cond, int cond_ld,
+                                 int shift_off, int scale_off, const int * __restrict__ row_utt, void * out16,
+                                 int out_dtype, float * out32) {
+    constexpr int DIM = NV * 128;
+    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int lane = threadIdx.x & 31;
+    const int utt = row_utt ? row_utt[row] : 0;
+    const float4 * xr = reinterpret_cast<const float4 *>(x + (size_t) row * DIM);
+    float4 v[NV];
+    float s = 0.0f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        v[i] = xr[lane + 32 * i];
+        s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+    }
+    const float mean = warp_sum(s) * (1.0f / DIM);
+    float q = 0.0f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        v[i].x -= mean; v[i].y -= mean; v[i].z -= mean; v[i].w -= mean;
+        q += (v[i].x * v[i].x + v[i].y * v[i].y) + (v[i].z * v[i].z + v[i].w * v[i].w);
+    }
+    const float var = warp_sum(q) * (1.0f / DIM);
+    const float rstd = 1.0f / sqrtf(var + eps);
+    const float * shift = cond ? cond + (size_t) max(utt, 0) * cond_ld + shift_off : nullptr;
+    const float * scale = cond ? cond + (size_t) max(utt, 0) * cond_ld + scale_off : nullptr;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        const int c4 = lane + 32 * i;
+        float4 y = make_float4(v[i].x * rstd, v[i].y * rstd, v[i].z * rstd, v[i].w * rstd);
+        if (cond) {
+            const float4 sc = __ldg(reinterpret_cast<const float4 *>(scale) + c4);
+            const float4 sh = __ldg(reinterpret_cast<const float4 *>(shift) + c4);
+            y.x = y.x * (sc.x + 1.0f) + sh.x; y.y = y.y * (sc.y + 1.0f) + sh.y;
+            y.z = y.z * (sc.z + 1.0f) + sh.z; y.w = y.w * (sc.w + 1.0f) + sh.w;
+        } else if (w) {
+            const float4 ww = __ldg(reinterpret_cast<const float4 *>(w) + c4);
+            const float4 bb = __ldg(reinterpret_cast<const float4 *>(b) + c4);
+            y.x = y.x * ww.x + bb.x; y.y = y.y * ww.y + bb.y; y.z = y.z * ww.z + bb.z; y.w = y.w * ww.w + bb.w;
+        }
+        if (utt < 0) y = make_float4(0.f, 0.f, 0.f, 0.f);   // gap row of the layout
+        if (out32) reinterpret_cast<float4 *>(out32 + (size_t) row * DIM)[c4] = y;
+        if (out16) {
+            uint2 o;
+            o.x = pack16(y.x, y.y, out_dtype);
+            o.y = pack16(y.z, y.w, out_dtype);
+            reinterpret_cast<uint2 *>((uint16_t *) out16 + (size_t) row * DIM)[c4] = o;
+        }
+    }
+}
+
+// generic-width fallback (dim % 128 != 0 or dim > 1024): one warp per row, three passes over the row
+__global__ void layernorm_generic_kernel(const float * __restrict__ x, int rows, int dim, float eps,
+                                         const float * __restrict__ w, const float * __restrict__ b,
+                                         const float * __restrict__ cond, int cond_ld, int shift_off, int scale_off,
+                                         const int * __restrict__ row_utt, void * out16, int out_dtype,
+                                         float * out32) {
+    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int lane = threadIdx.x & 31;
+    const int utt = row_utt ? row_utt[row] : 0;
+    const float * xr = x + (size_t) row * dim;
+    float s = 0.0f;
+    for (int i = lane; i < dim; i += 32) s += xr[i];
+    const float mean = warp_sum(s) / (float) dim;
+    float q = 0.0f;
+    for (int i = lane; i < dim; i += 32) { const float d = xr[i] - mean; q += d * d; }
+    const float rstd = 1.0f / sqrtf(warp_sum(q) / (float) dim + eps);
+    const float * shift = cond ? cond + (size_t) max(utt, 0) * cond_ld + shift_off : nullptr;
+    const float * scale = cond ? cond + (size_t) max(utt, 0) * cond_ld + scale_off : nullptr;
+    for (int i = lane; i < dim; i += 32) {
+        float y = (xr[i] - mean) * rstd;
+        if (cond) y = y * (scale[i] + 1.0f) + shift[i];
+        else if (w) y = y * w[i] + b[i];
+        if (utt < 0) y = 0.0f;
+        if (out32) out32[(size_t) row * dim + i] = y;
+        if (out16) ((uint16_t *) out16)[(size_t) row * dim + i] = (uint16_t) (pack16(y, 0.f, out_dtype) & 0xFFFF);
+    }
+}
+
+__global__ void cast16_kernel(const float * __restrict__ x, void * out16, int out_dtype, size_t n4) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n4) return;
+    const float4 v = reinterpret_cast<const float4 *>(x)[i];
+    uint2 o;
+    o.x = pack16(v.x, v.y, out_dtype);
+    o.y = pack16(v.z, v.w, out_dtype);
+    reinterpret_cast<uint2 *>(out16)[i] = o;
+}
+
+// ---- GroupNorm phase 1: per (utterance, group) sum and sum of squares over (channels-in-group x ALL frames)
+//      (ggml_group_norm, ggml-cpu/ops.cpp:3955-4028: double accumulators).  One block per <=64-row tile. ----
+template <int VEC>
+__global__ void gn_stats_kernel(const float * __restrict__ x, int dim, int groups, const row_tile * __restrict__ tiles,
+                                double * __restrict__ stats) {
+    extern __shared__ double s_acc[];   // [groups][2]
+    const row_tile t = tiles[blockIdx.x];
+    for (int i = threadIdx.x; i < groups * 2; i += blockDim.x) s_acc[i] = 0.0;
+    __syncthreads();
+    const int cpg = dim / groups;
+    const int cols = dim / VEC;                       // column slots per row
+    const int rows_per_pass = blockDim.x / cols > 0 ? blockDim.x / cols : 1;
+    const int col = threadIdx.x % cols;
+    const int ry = threadIdx.x / cols;
+    if (ry < rows_per_pass) {
+        float s = 0.0f, q = 0.0f;
+        for (int r = ry; r < t.n; r += rows_per_pass) {
+            const float * p = x + (size_t) (t.row0 + r) * dim + col * VEC;
+            if constexpr (VEC == 4) {
+                const float4 v = *reinterpret_cast<const float4 *>(p);
+                s += (v.x + v.y) + (v.z + v.w);
+                q += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
+            } else {
+                const float v = *p;
+                s += v; q += v * v;
+            }
+        }
+        const int g = (col * VEC) / cpg;
+        atomicAdd(&s_acc[2 * g], (double) s);
+        atomicAdd(&s_acc[2 * g + 1], (double) q);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < groups * 2; i += blockDim.x)
+        atomicAdd(&stats[(size_t) t.utt * groups * 2 + i], s_acc[i]);
+}
+
+__global__ void gn_finalize_kernel(const double * __restrict__ stats, const int * __restrict__ utt_len, int cpg,
+                                   int groups, int n_utt, float eps, float2 * __restrict__ mr) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_utt * groups) return;
+    const double n = (double) utt_len[i / groups] * (double) cpg;
+    const double mean = stats[2 * i] / n;
+    double var = stats[2 * i + 1] / n - mean * mean;
+    if (var < 0.0) var = 0.0;
+    mr[i] = make_float2((float) mean, 1.0f / sqrtf((float) var + eps));
+}
+
+// ---- GroupNorm phase 2: normalise, affine, SiLU, round to the conv operand type (fp16, as the reference's
+//      im2col does: llama.cpp/ggml/src/ggml.c:4409-4426), zero the layout's gap rows. ----
+__global__ void gn_apply_kernel(const float * __restrict__ x, int rows, int dim, int groups,
+                                const float2 * __restrict__ mr, const float * __restrict__ w,
+                                const float * __restrict__ b, const int * __restrict__ row_utt, void * out16,
+                                int out_dtype) {
+    const int c4n = dim >> 2;
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t) rows * c4n) return;
+    const int row = (int) (i / c4n);
+    const int c4 = (int) (i % c4n);
+    const int utt = row_utt[row];
+    uint2 o = make_uint2(0u, 0u);
+    if (utt >= 0) {
+        const int cpg = dim / groups;
+        const float4 v = reinterpret_cast<const float4 *>(x)[i];
+        const float4 ww = __ldg(reinterpret_cast<const float4 *>(w) + c4);
+        const float4 bb = __ldg(reinterpret_cast<const float4 *>(b) + c4);
+        float y[4] = {v.x, v.y, v.z, v.w};
+        const float wv[4] = {ww.x, ww.y, ww.z, ww.w};
+        const float bv[4] = {bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float2 m = __ldg(mr + (size_t) utt * groups + (c4 * 4 + k) / cpg);
+            const float t = ((y[k] - m.x) * m.y) * wv[k] + bv[k];
+            y[k] = silu_exact(t);
+        }
+        o.x = pack16(y[0], y[1], out_dtype);
+        o.y = pack16(y[2], y[3], out_dtype);
+    }
+    reinterpret_cast<uint2 *>(out16)[i] = o;
+}
+
+// ---- ggml_interpolate(BILINEAR) along frames only: half-pixel centres, clamped taps
+//      (ggml-cpu/ops.cpp:7577-7617, call src/miocodec-decoder.cpp:1373); identity when lengths match. ----
+__global__ void interp_kernel(const float * __restrict__ src, const int * __restrict__ src_row0,
+                              const int * __restrict__ src_len, float * __restrict__ dst, int rows, int dim,
+                              const int * __restrict__ row_utt, const int * __restrict__ row_pos,
+                              const int * __restrict__ utt_len) {
+    const int c4n = dim >> 2;
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t) rows * c4n) return;
+    const int row = (int) (i / c4n);
+    const int c4 = (int) (i % c4n);
+    const int utt = row_utt[row];
+    float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (utt >= 0) {
+        const int L = src_len[utt], n_out = utt_len[utt], p = row_pos[row];
+        const float4 * s4 = reinterpret_cast<const float4 *>(src);
+        if (L == n_out) {
+            o = s4[(size_t) (src_row0[utt] + p) * c4n + c4];
+        } else {
+            const float sf = (float) n_out / (float) L;
+            const float xs = ((float) p + 0.5f) / sf - 0.5f;
+            int x0 = (int) floorf(xs);
+            int x1 = x0 + 1;
+            x0 = min(max(x0, 0), L - 1);
+            x1 = min(max(x1, 0), L - 1);
+            float dx = xs - (float) x0;
+            dx = fminf(fmaxf(dx, 0.0f), 1.0f);
+            const float4 a = s4[(size_t) (src_row0[utt] + x0) * c4n + c4];
+            const float4 c = s4[(size_t) (src_row0[utt] + x1) * c4n + c4];
+            o.x = a.x * (1.0f - dx) + c.x * dx; o.y = a.y * (1.0f - dx) + c.y * dx;
+            o.z = a.z * (1.0f - dx) + c.z * dx; o.w = a.w * (1.0f - dx) + c.w * dx;
+        }
+    }
+    reinterpret_cast<float4 *>(dst)[i] = o;
+}
+
+// ---- RoPE cache: theta_i = pos * s^i by repeated fp32 multiplication (ggml-cpu/ops.cpp:5616-5625) ----
+__global__ void rope_table_kernel(float2 * __restrict__ table, int n_pos, int half_dim, float theta_scale) {
+    const int pos = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pos >= n_pos) return;
+    float theta = (float) pos;
+    for (int i = 0; i < half_dim; ++i) {
+        table[(size_t) pos * half_dim + i] = make_float2(cosf(theta), sinf(theta));
+        theta *= theta_scale;
+    }
+}
+
+// ---- wave-upsampler stage: fold (col2im) of ggml_conv_transpose_1d computed as a [rows, k*Cout] GEMM,
+//      + bias, crop pad=(k-s)/2 per side, SnakeBeta (src/miocodec-decoder.cpp:1410-1442, :1332-1343). ----
+__global__ void convt_fold_snake_kernel(const float * __restrict__ y, int ld_y, const int * __restrict__ src_row0,
+                                        const int * __restrict__ src_len, float * __restrict__ dst, int rows, int cout,
+                                        int ksize, int stride, int pad, const float * __restrict__ bias,
+                                        const float * __restrict__ snake_a, const float * __restrict__ snake_inv_b,
+                                        const int * __restrict__ row_utt, const int * __restrict__ row_pos) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t) rows * cout) return;
+    const int row = (int) (i / cout);
+    const int co = (int) (i % cout);
+    const int utt = row_utt[row];
+    float o = 0.0f;
+    if (utt >= 0) {
+        const int t = row_pos[row] + pad;
+        const int L = src_len[utt];
+        float acc = 0.0f;
+        // out[t] = sum over (l, kk) with l*stride + kk == t; ascending l like the reference's accumulation
+        const int l_hi = min(L - 1, t / stride);
+        int l_lo = (t - ksize + stride) / stride;   // ceil((t - ksize + 1) / stride) for t-ksize+1 >= 0
+        if (t - ksize + 1 <= 0) l_lo = 0;
+        for (int l = l_lo; l <= l_hi; ++l) {
+            const int kk = t - l * stride;
+            if (kk >= 0 && kk < ksize) acc += y[(size_t) (src_row0[utt] + l) * ld_y + (size_t) kk * cout + co];
+        }
+        acc += bias[co];
+        const float s = sinf(acc * snake_a[co]);
+        o = acc + (s * s) * snake_inv_b[co];
+    }
+    dst[i] = o;
+}
+
+__global__ void snake_kernel(float * __restrict__ x, int rows, int dim, const float * __restrict__ snake_a,
+                             const float * __restrict__ snake_inv_b) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t) rows * dim) return;
+    const int c = (int) (i % dim);
+    const float v = x[i];
+    const float s = sinf(v * snake_a[c]);
+    x[i] = v + (s * s) * snake_inv_b[c];
+}
+
+inline unsigned blocks_for(size_t n, int threads) { return (unsigned) ((n + threads - 1) / threads); }
+
+} // namespace
+
+void launch_gather(const float * table, const int * codes, float * out, int n_rows, int dim, cudaStream_t st) {
+    if (n_rows <= 0) return;
+    gather_kernel<<<blocks_for((size_t) n_rows, 8), 256, 0, st>>>(table, codes, out, n_rows, dim);
+    MIO_CUDA(cudaGetLastError());
+    count_launch();
+}
+
+void launch_cond(const float * w, const float * b, const float * emb, float * out, int n_out, int adim, int n_utt,
+                 cudaStream_t st) {
+    if (n_out <= 0 || n_utt <= 0) return;
+    dim3 grid(blocks_for((size_t) n_out, 8), (unsigned) n_utt);
+    cond_kernel<<<grid, 256, 0, st>>>(w, b, emb, out, n_out, adim);
+    MIO_CUDA(cudaGetLastError());
+    count_launch();
+}
+
+void launch_layernorm(const float * x, int rows, int dim, float eps, const float * w, const float * b,
+                      const float * cond, int cond_ld, int shift_off, int scale_off, const int * row_utt,
+                      void * out16, int out_dtype, float * out32, cudaStream_t st) {
+    if (rows <= 0) return;
+    const unsigned grid = blocks_for((size_t) rows, 8);
+#define LN_CASE(NV)                                                                                              \
+    case NV:                                                                                                     \
+        layernorm_kernel<NV><<<grid, 256, 0, st>>>(x, rows, eps, w, b, cond, cond_ld, shift_off, scale_off,      \
+                                                   row_utt, out16, out_dtype, out32);                            \
+        break;
+    if ((dim % 128) == 0 && dim <= 1024 && (!cond || ((cond_ld | shift_off | scale_off) & 3) == 0)) {
+        switch (dim / 128) {
+            LN_CASE(1) LN_CASE(2) LN_CASE(3) LN_CASE(4) LN_CASE(5) LN_CASE(6) LN_CASE(7) LN_CASE(8)
+        }
+    } else {
+        layernorm_generic_kernel<<<grid, 256, 0, st>>>(x, rows, dim, eps, w, b, cond, cond_ld, shift_off, scale_off,
+                                                       row_utt, out16, out_dtype, out32);
+    }
+#undef LN_CASE
+    MIO_CUDA(cudaGetLastError());
+    count_launch();
+}
+
+void launch_cast16(const float * x, void * out16, int out_dtype, size_t n, cudaStream_t st) {
+    if (n == 0) return;
+    if (n & 3) throw cuda_error("cast16: element count must be a multiple of 4");
+    cast16_kernel<<<blocks_for(n >> 2, 256), 256, 0, st>>>(x, out16, out_dtype, n >> 2);
+    MIO_CUDA(cudaGetLastError());
+    count_launch();
+}
+
+void launch_gn_stats(const float * x, int dim, int groups, const row_tile * tiles, int n_tiles, double * stats,
+                     cudaStream_t st) {
+    if (n_tiles <= 0) return;
+    const int cpg = dim / groups;
+    const size_t smem = (size_t) groups * 2 * sizeof(double);
+    if ((cpg & 3) == 0) {
+        const int cols = dim / 4;
+        const int threads = cols >= 256 ? ((cols + 31) / 32) * 32 : 256;
+        gn_stats_kernel<4><<<n_tiles, threads > 1024 ? 1024 : threads, smem, st>>>(x, dim, groups, tiles, stats);
+    } else {
+        const int threads = dim >= 256 ? ((dim + 31) / 32) * 32 : 256;
+        gn_stats_kernel<1><<<n_tiles, threads > 1024 ? 1024 : threads, smem, st>>>(x, dim, groups, tiles, stats);
+    }
+    MIO_CUDA(cudaGetLastError());
+    count_launch();
+}
+
+void launch_gn_apply(const float * x, int rows, int dim, int groups, const float2 * mean_rstd, const float * w,
+                     const float * b, const int * row_utt, void * out16, int out_dtype, cudaStream_t st) {
+    if (rows <= 0) return;
+    if (dim & 3) throw cuda_error("group norm: channel count must be a multiple of 4");
+    gn_apply_kernel<<<blocks_for((size_t) rows * (dim >> 2), 256), 256, 0, st>>>(
+        x, rows, dim, groups, mean_rstd, w, b, row_utt, out16, out_dtype);
+    MIO_CUDA(cudaGetLastError());
+    count_launch();
+}
+
+void launch_gn_finalize(const double * stats, const int * utt_len, int cpg, int groups, int n_utt, float eps,
+                        float2 * mr, cudaStream_t st) {
+    gn_finalize_kernel<<<blocks_for((size_t) n_utt * groups, 128), 128, 0, st>>>(stats, utt_len, cpg, groups, n_utt,
+                                                                               eps, mr);
+    MIO_CUDA(cudaGetLastError());
+    count_launch();
+}
+
+void launch_interp(const float * src, const int * src_row0, const int * src_len, float * dst, int rows, int dim,
+                   const int * row_utt, const int * row_pos, const int * utt_len, cudaStream_t st) {
+    if (rows <= 0) return;
+    if (dim & 3) throw cuda_error("interp: channel count must be a multiple of 4");
+    interp_kernel<<<blocks_for((size_t) rows * (dim >> 2), 256), 256, 0, st>>>(src, src_row0, src_len, dst, rows, dim,
+                                                                               row_utt, row_pos, utt_len);
+    MIO_CUDA(cudaGetLastError());
+    count_launch();
+}
+
+void launch_rope_table(float2 * table, int n_pos, int half_dim, float theta_scale, cudaStream_t st) {
+    if (n_pos <= 0) return;
+    rope_table_kernel<<<blocks_for((size_t) n_pos, 128), 128, 0, st>>>(table, n_pos, half_dim, theta_scale);
+    MIO_CUDA(cudaGetLastError());
+    count_launch();
+}
+
+void launch_convt_fold_snake(const float * y, int ld_y, const int * src_row0, const int * src_len, float * dst,
+                             int rows, int cout, int ksize, int stride, int pad, const float * bias,
+                             const float * snake_a, const float * snake_inv_b, const int * row_utt,
+                             const int * row_pos, cudaStream_t st) {
+    if (rows <= 0) return;
+    convt_fold_snake_kernel<<<blocks_for((size_t) rows * cout, 256), 256, 0, st>>>(
+        y, ld_y, src_row0, src_len, dst, rows, cout, ksize, stride, pad, bias, snake_a, snake_inv_b, row_utt, row_pos);
+    MIO_CUDA(cudaGetLastError());
+    count_launch();
+}
+
+void launch_snake(float * x, int rows, int dim, const float * snake_a, const float * snake_inv_b, cudaStream_t st) {
+    if (rows <= 0) return;
+    snake_kernel<<<blocks_for((size_t) rows * dim, 256), 256, 0, st>>>(x, rows, dim, snake_a, snake_inv_b);
+    MIO_CUDA(cudaGetLastError());
+    count_launch();
+}
+
+} // namespace mio
