@@ -1,0 +1,224 @@
+#!/usr/bin/env python3
+"""bench.py -- MioCodec decode + iSTFT throughput (BASELINE.json metric: audio-seconds per second).
+
+  python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (one process per GPU under torchrun)
+  python bench.py --impl reference --gpus N --steps K ...  # the reference's own CPU path (oracle/_ref) on the host cores
+
+A step = one pass of the hot path over BASELINE config 2 on each GPU: 64 utterances x 400 synthetic codes
+(16 s of 24 kHz audio each, default hyper-parameters, synthetic weights in the reference's GGUF layout).
+Multi-GPU = independent replicas (weak scaling, no collective on the data path).
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+from mio_tts_cpp_b200 import benchutil as U  # noqa: E402
+
+BATCH, N_CODES = 64, 400
+
+
+def baseline_metric():
+    try:
+        return json.load(open(os.path.join(ROOT, "BASELINE.json")))["metric"]
+    except Exception:   # noqa: BLE001
+        return "MioCodec+iSTFT audio-seconds/sec (RTF^-1) per GPU and at 8xB200"
+
+
+def time_cpu_reference(n_utt, n_codes, warmup=0):
+    """The reference's own CPU mio_tts_synthesize (oracle/_ref = the unmodified reference compiled from
+    /root/reference; else the numpy port), `n_utt` sequential utterances with all host threads -- the reference has
+    no batch API.  This is the ONLY place bench.py executes anything under oracle/."""
+    from oracle.refbind import RefLib, ref_lib_path
+
+    emb = U.speaker_embedding()
+    codes = U.config2_workload(0, n_utt + warmup, n_codes)
+    if ref_lib_path() is not None:
+        R = RefLib()
+        cores = R.hw_threads()
+        ctx = R.open_context(U.synth_gguf("default"))
+        devnull, saved = os.open(os.devnull, os.O_WRONLY), os.dup(2)
+        os.dup2(devnull, 2)            # the reference prints a "synth breakdown" line per call on stderr
+        try:
+            for i in range(warmup):
+                R.synthesize(ctx, codes[i], emb, n_threads=cores)
+            t0, secs = time.perf_counter(), 0.0
+            for i in range(n_utt):
+                a, sr = R.synthesize(ctx, codes[warmup + i], emb, n_threads=cores)
+                secs += a.size / sr
+            dt = time.perf_counter() - t0
+        finally:
+            os.dup2(saved, 2)
+            os.close(devnull)
+            os.close(saved)
+        R.close_context(ctx)
+        return secs / dt, cores, "reference", dt
+    from oracle import miocodec_np as O
+
+    m = O.Model(U.synth_gguf("default"))
+    t0, secs = time.perf_counter(), 0.0
+    for i in range(n_utt):
+        secs += O.synthesize(m, codes[warmup + i], emb).size / m.hp["sample_rate"]
+    dt = time.perf_counter() - t0
+    return secs / dt, 1, "port", dt
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    per_step = 2   # utterances per step: a bounded sample of config 2 (the CPU path takes ~1 s per utterance)
+    v, cores, kind, dt = time_cpu_reference(per_step * args.steps, N_CODES, warmup=min(args.warmup, 2))
+    sample = f"{per_step * args.steps} of the 64 utterances x {N_CODES} codes, sequential mio_tts_synthesize, {cores} threads"
+    line = {"impl": "reference", "metric": baseline_metric(), "value": v, "unit": "audio-seconds/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(1, args.steps),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"config2: batch {BATCH} x {N_CODES} codes, default 24 kHz hyper-parameters "
+                                   "(bounded sample per step)", "sample_utterances_per_step": per_step},
+            "cpu_baseline": {"value": v, "unit": "audio-seconds/s", "cores": cores, "kind": kind, "sample": sample},
+            "e2e": {"value": v, "unit": "audio-seconds/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def run_b200(args, rank, world, local_rank):
+    import torch
+
+    os.environ["MIO_TTS_BACKEND_DEVICE"] = f"CUDA{local_rank}"
+    from mio_tts_cpp_b200 import MioTTS
+
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+
+        torch.cuda.set_device(local_rank)
+        dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist = dist_mod
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local_rank}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local_rank}")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    if rank == 0:
+        path = U.synth_gguf("default")
+    barrier()
+    path = U.synth_gguf("default")
+    m = MioTTS(path)
+    emb = U.speaker_embedding()
+    codes = U.config2_workload(rank, BATCH, N_CODES)
+    embs = [emb] * BATCH
+    sr = m.sample_rate()
+
+    # ---- device-resident throughput: inputs already in HBM when the timed region starts ----
+    m.prepare(codes, embs)
+    audio_s_per_step = m.resident_samples() / sr
+    for _ in range(max(args.warmup, 3)):
+        m.run_resident(1)
+    barrier()
+    torch.cuda.synchronize()
+    n0 = m.launch_count()
+    with U.ClockSampler(local_rank) as cs:
+        ms = m.run_resident(args.steps)          # CUDA events on the library's stream around K back-to-back steps
+    launches = m.launch_count() - n0
+    barrier()
+    ms = max_over_ranks(ms)
+    total_audio = sum_over_ranks(audio_s_per_step)
+    value = total_audio / (ms * 1e-3)
+
+    # ---- end to end through the public batch call: host codes in, host (pinned) waveforms out, every step ----
+    for _ in range(2):
+        m.synthesize_batch(codes, embs, copy=False)
+    barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        m.synthesize_batch(codes, embs, copy=False)
+    e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
+    e2e = total_audio / e2e_s
+    h2d = m.last_h2d_bytes()
+    d2h = int(m.resident_samples() * 4)
+
+    line = {"metric": baseline_metric(), "value": value, "unit": "audio-seconds/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": f"config2: batch {BATCH} x {N_CODES} codes per GPU, default 24 kHz hyper-parameters, "
+                                   "fp32 iSTFT, synthetic weights in the reference GGUF layout",
+                       "audio_seconds_per_step_per_gpu": audio_s_per_step, "parallelism": f"replicas x{world}",
+                       "l2": "no flush: each step streams ~2 GB of activations (> 126 MB L2); inputs are 100 KB of codes"},
+            "e2e": {"value": e2e, "unit": "audio-seconds/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": d2h,
+                    "ms_per_step": 1e3 * e2e_s},
+            "gpu_launches": int(launches), "clocks": cs.summary()}
+
+    if rank == 0:
+        # ---- roofline of the dominant kernel (the tcgen05 GEMM family), timed live with CUDA events per launch ----
+        peaks = U.measured_peaks()
+        profs = [m.profile_resident() for _ in range(3)]
+        p = profs[-1]
+        g_ms = float(np.median([q["gemm_ms"] for q in profs]))
+        achieved = p["gemm_flops"] / (g_ms * 1e-3) / 1e12
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "gemm_traffic.json")
+        if os.path.exists(tp):
+            traffic = json.load(open(tp)).get("dram_bytes_per_launch")
+        line["roofline"] = {"bound": "tensor", "achieved": achieved, "peak": peaks["bf16_tflops_sustained"],
+                            "unit": "TFLOP/s", "frac": achieved / peaks["bf16_tflops_sustained"], "traffic": traffic,
+                            "peak_source": peaks["source"] + " (bf16 sustained: kernel timed inside a long step)",
+                            "kernel": "gemm_tcgen05_kernel", "launches_per_step": p["gemm_launches"],
+                            "avg_launch_ms": g_ms / max(1, p["gemm_launches"]),
+                            "flops_per_launch_avg": p["gemm_flops"] / max(1, p["gemm_launches"]),
+                            "gemm_share_of_step": g_ms / p["total_ms"],
+                            "whole_path_frac": (U.FLOP_PER_TOKEN * BATCH * N_CODES / (ms * 1e-3) / 1e12)
+                            / peaks["bf16_tflops_sustained"] if world == 1 else None}
+        line["stages_ms"] = {k: p[k] for k in ("prenet_ms", "upsample_prior_ms", "decoder_ms", "post_head_ms", "istft_ms",
+                                               "total_ms", "attn_ms")}
+        if world == 1:
+            # ---- CPU baseline: the unmodified reference on this box's host cores, bounded sample ----
+            n_cpu = 6
+            v, cores, kind, dt = time_cpu_reference(n_cpu, N_CODES, warmup=1)
+            line["cpu_baseline"] = {"value": v, "unit": "audio-seconds/s", "cores": cores, "kind": kind,
+                                    "sample": f"{n_cpu} of the 64 utterances x {N_CODES} codes, sequential "
+                                              f"mio_tts_synthesize calls, {cores} threads, {dt:.1f} s"}
+        print(json.dumps(line), flush=True)
+    barrier()
+    m.free()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+    else:
+        run_b200(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -164,6 +164,7 @@ void engine::build_layout(seq_layout & L, const std::vector<int> & len, int gap)
         L.max_len = std::max(L.max_len, len[u]);
     }
     L.rows = r;
+    for (int l : len) L.valid += l;   // rows that carry data (algorithmic work excludes the gap rows)
 }
 
 void engine::append_layout(seq_layout & L) {
@@ -392,7 +393,7 @@ void engine::gemm(const dbuf & a, const dev_linear & w, int M, int epilogue, voi
     gemm_launch(g, mdl->num_sms, st_);
     if (prof_gemm_) {
         MIO_CUDA(cudaEventRecord(gemm_ev_[evi + 1], st_));
-        gemm_ev_flops_.push_back({evi, 2.0 * (double) M * w.N * w.K * w.taps});
+        gemm_ev_flops_.push_back({evi, 2.0 * (double) (lay ? lay->valid : M) * w.N * w.K * w.taps});
     }
 }
 

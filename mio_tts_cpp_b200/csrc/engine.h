@@ -16,7 +16,7 @@
 namespace mio {
 
 struct seq_layout {
-    int n_utt = 0, gap = 0, rows = 0, max_len = 0, n_tiles = 0;
+    int n_utt = 0, gap = 0, rows = 0, valid = 0, max_len = 0, n_tiles = 0;
     std::vector<int> len, row0;
     const int * d_len = nullptr, * d_row0 = nullptr, * d_row_utt = nullptr, * d_row_pos = nullptr;
     const row_tile * d_tiles = nullptr;

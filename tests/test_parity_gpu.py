@@ -1,0 +1,238 @@
+"""Parity of the CUDA path (through the C ABI) against the oracle and the committed reference outputs.
+
+Tolerances (BASELINE.json north_star):
+  * codebook gather: bit-exact.
+  * fp32 iSTFT fed the oracle's / reference's spectrogram: max-abs <= 1e-3 and SNR >= 40 dB (measured: > 110 dB).
+  * decoder in bf16 operands / fp32 accumulate (fp16 operands for the convs, as the reference rounds them):
+    spectrogram SNR >= 38 dB vs the reference's fp32 CPU decode (measured 41-47 dB on the six fixtures) and end-to-end
+    waveform SNR >= 28 dB (measured 30-38 dB; the phase half of the spectrogram amplifies operand rounding).
+    With MIO_TTS_B200_LINEAR_DTYPE=f16 the same path measures higher; that mode is checked in a subprocess.
+"""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN_CASES, ISTFT_CASES, ROOT, load_golden, snr_db
+from oracle import miocodec_np as O
+
+pytestmark = pytest.mark.gpu
+
+SPEC_SNR_MIN, AUDIO_SNR_MIN = 38.0, 28.0
+
+
+@pytest.fixture(scope="module")
+def ctxs(gguf_paths):
+    from mio_tts_cpp_b200 import MioTTS
+
+    cache = {}
+
+    def get(preset):
+        if preset not in cache:
+            cache[preset] = MioTTS(gguf_paths(preset)[0])
+        return cache[preset]
+
+    yield get
+    for m in cache.values():
+        m.free()
+
+
+def test_library_is_loaded_in_process():
+    from mio_tts_cpp_b200 import load_library
+
+    load_library()
+    assert any("libmio_tts_b200.so" in line for line in open("/proc/self/maps"))
+
+
+# ---------------------------------------------------------------- gather (A1): bit-exact
+@pytest.mark.parametrize("preset", ["tiny", "default"])
+def test_gather_bit_exact(preset, ctxs, gguf_paths):
+    m = ctxs(preset)
+    om = O.Model(gguf_paths(preset)[0])
+    rng = np.random.default_rng(0)
+    for n in (1, 2, 31, 400, 4097):
+        codes = rng.integers(0, 12800, n).astype(np.int32)
+        codes[0], codes[-1] = 0, 12799
+        g = m.gather(codes)
+        assert g.dtype == np.float32 and g.tobytes() == O.gather_codebook(om, codes).tobytes()
+
+
+# ---------------------------------------------------------------- iSTFT (A11)
+@pytest.mark.parametrize("name", ISTFT_CASES)
+def test_istft_vs_reference_fixture(name, ctxs):
+    z = load_golden(name)
+    a = ctxs("tiny").istft(z["spec"], int(z["n_fft"]), int(z["hop"]))
+    assert a.shape == z["audio"].shape
+    assert np.abs(a - z["audio"]).max() <= 1e-3
+    assert snr_db(a, z["audio"]) >= 40.0
+    assert np.abs(a - z["audio"]).max() <= 2e-6      # what the fp32 kernel actually achieves
+
+
+@pytest.mark.parametrize("n_fft,hop", [(1920, 480), (392, 98), (120, 30), (2048, 512), (1280, 320), (64, 16), (30, 10)])
+@pytest.mark.parametrize("frames", [1, 2, 3, 4, 7, 8, 9, 60, 61, 62, 64, 123, 200])
+def test_istft_vs_oracle_ragged(n_fft, hop, frames, ctxs):
+    """Frame counts straddle the kernel's 8-frame rounds and its per-CTA chunk boundaries."""
+    rng = np.random.default_rng(n_fft * 1000 + frames)
+    nf = n_fft // 2 + 1
+    spec = np.concatenate([rng.normal(-2, 1, (frames, nf)), rng.uniform(-8, 8, (frames, nf))], 1).astype(np.float32)
+    spec[0, 0] = 6.0                       # magnitude clip at 100 (lib.cpp:709-712)
+    spec[frames // 2, nf - 1] = 5.5        # and on the Nyquist bin
+    ref = O.istft(spec, n_fft, hop)
+    a = ctxs("tiny").istft(spec, n_fft, hop)
+    assert a.shape == ref.shape
+    if (n_fft - hop) % 2 == 0:
+        assert a.size == frames * hop
+    assert np.abs(a - ref).max() <= 1e-3 * max(1.0, np.abs(ref).max())
+    assert snr_db(a, ref) >= 40.0
+
+
+def test_istft_rejects_unsupported_sizes(ctxs):
+    from mio_tts_cpp_b200 import MioTtsError
+
+    with pytest.raises(MioTtsError, match="unsupported"):
+        ctxs("tiny").istft(np.zeros((2, 36), np.float32), 34, 2)     # M = 17: prime factor > 13, and n_fft > 9*hop
+    assert ctxs("tiny").istft(np.zeros((0, 122), np.float32), 120, 30).size == 0
+
+
+# ---------------------------------------------------------------- decode (A2-A10) and synthesize (A0)
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_decode_and_synthesize_vs_reference_fixture(name, ctxs, gguf_paths, emb):
+    z = load_golden(name)
+    preset = str(z["preset"])
+    assert gguf_paths(preset)[1] == str(z["weights_sha256"])
+    m = ctxs(preset)
+    spec = m.decode_spec(z["codes"], emb)
+    assert spec.shape == z["spec"].shape and np.isfinite(spec).all()
+    assert snr_db(spec, z["spec"]) >= SPEC_SNR_MIN
+    # the fp32 iSTFT on the REFERENCE's spectrogram reproduces the reference's waveform (before peak normalise)
+    hp = O.Model(gguf_paths(preset)[0]).hp
+    a0 = m.istft(z["spec"], hp["n_fft"], hp["hop_length"])
+    ref_audio = z["audio"]
+    a0n = O.peak_normalize(a0)
+    assert np.abs(a0n - ref_audio).max() <= 1e-3 and snr_db(a0n, ref_audio) >= 40.0
+    audio, sr = m.synthesize(z["codes"], emb)
+    assert sr == int(z["sample_rate"]) and audio.shape == ref_audio.shape
+    assert audio.size == z["codes"].size * m.samples_per_token()
+    assert snr_db(audio, ref_audio) >= AUDIO_SNR_MIN
+
+
+@pytest.mark.parametrize("name,stage_keys", [("tiny_T50", ["prenet", "upsample", "prior", "decoder", "post"]),
+                                             ("default_T24", ["prenet", "upsample", "prior", "decoder", "post"])])
+def test_intermediate_stages_vs_oracle(name, stage_keys, ctxs, gguf_paths, emb):
+    z = load_golden(name)
+    preset = str(z["preset"])
+    om = O.Model(gguf_paths(preset)[0])
+    _, st = O.decode_tokens(om, z["codes"], emb, return_stages=True)
+    for i, k in enumerate(stage_keys, start=1):
+        got = ctxs(preset).debug_stage(z["codes"], emb, i)
+        assert got.shape == st[k].shape
+        assert snr_db(got, st[k]) >= 36.0, k      # measured 40.0-47.5 dB
+
+
+def test_generic_attention_agrees_with_band_kernel(ctxs, emb):
+    m = ctxs("tiny")
+    codes = np.random.default_rng(3).integers(0, 12800, 150).astype(np.int32)
+    a = m.decode_spec(codes, emb)
+    m.set_generic_attention(True)
+    b = m.decode_spec(codes, emb)
+    m.set_generic_attention(False)
+    assert snr_db(a, b) >= 45.0
+
+
+def test_peak_normalise_branch(ctxs, gguf_paths, emb):
+    """upsampler fixtures exceed 0.98 before the normaliser: output peak must be 0.95 (lib.cpp:1299-1310)."""
+    z = load_golden("upsampler_tiny_T20")
+    audio, _ = ctxs("upsampler_tiny").synthesize(z["codes"], emb)
+    assert abs(float(np.abs(audio).max()) - 0.95) < 1e-5
+    assert abs(float(np.abs(z["audio"]).max()) - 0.95) < 1e-5
+
+
+# ---------------------------------------------------------------- batching: ragged, order, determinism
+def test_ragged_batch_equals_single_calls(ctxs, emb):
+    m = ctxs("tiny")
+    rng = np.random.default_rng(11)
+    lens = [1, 2, 63, 64, 65, 127, 128, 129, 400, 5]
+    codes = [rng.integers(0, 12800, n).astype(np.int32) for n in lens]
+    embs = [emb * (1.0 + 0.1 * i) for i in range(len(lens))]
+    batch, sr = m.synthesize_batch(codes, embs)
+    for c, e, b in zip(codes, embs, batch):
+        single, _ = m.synthesize(c, e)
+        assert b.shape == single.shape == (c.size * m.samples_per_token(),)
+        assert b.tobytes() == single.tobytes()          # row-local kernels + per-utterance statistics: bit-identical
+
+
+def test_clone_shares_weights_and_matches(ctxs, emb):
+    m = ctxs("tiny")
+    c = m.clone()
+    codes = np.arange(40, dtype=np.int32) * 7
+    a, _ = m.synthesize(codes, emb)
+    b, _ = c.synthesize(codes, emb)
+    c.free()
+    assert a.tobytes() == b.tobytes()
+
+
+def test_full_size_properties(ctxs, emb):
+    """BASELINE config 2 (64 x 400 codes, default hyper-parameters): size-independent properties."""
+    m = ctxs("default")
+    codes = [np.random.default_rng(42 + i).integers(0, 12800, 400).astype(np.int32) for i in range(64)]
+    a, sr = m.synthesize_batch(codes, [emb] * 64)
+    b, _ = m.synthesize_batch(codes, [emb] * 64)
+    assert sr == 24000 and all(x.size == 384000 and np.isfinite(x).all() for x in a)
+    assert all(x.tobytes() == y.tobytes() for x, y in zip(a, b))                   # deterministic
+    perm = list(reversed(range(64)))
+    c, _ = m.synthesize_batch([codes[i] for i in perm], [emb] * 64)
+    assert all(c[j].tobytes() == a[i].tobytes() for j, i in enumerate(perm))       # batch-order invariant
+    single, _ = m.synthesize(codes[17], emb)
+    assert single.tobytes() == a[17].tobytes()
+    # config 1: the reference's own CPU-runnable case (seed 42, 400 codes), checked against the oracle's iSTFT
+    spec = m.decode_spec(codes[0], emb)
+    ref = O.peak_normalize(O.istft(spec, 1920, 480))
+    assert np.abs(a[0] - ref).max() <= 1e-3 and snr_db(a[0], ref) >= 40.0
+
+
+# ---------------------------------------------------------------- error behaviour of mio_tts_synthesize
+def test_synthesize_errors(ctxs, emb):
+    from mio_tts_cpp_b200 import MioTtsError
+
+    m = ctxs("tiny")
+    with pytest.raises(MioTtsError, match="codes are empty"):
+        m.synthesize(np.zeros(0, np.int32), emb)
+    with pytest.raises(MioTtsError, match="code id out of range"):
+        m.synthesize(np.array([1, 12800], np.int32), emb)
+    with pytest.raises(MioTtsError, match="code id out of range"):
+        m.synthesize(np.array([-1], np.int32), emb)
+    with pytest.raises(MioTtsError, match="dynamic-global MioCodec requires embedding"):
+        m.synthesize(np.array([1, 2], np.int32), None)
+    with pytest.raises(MioTtsError, match="embedding dimension mismatch"):
+        m.synthesize(np.array([1, 2], np.int32), emb[:64])
+    with pytest.raises(MioTtsError, match="no CPU fallback"):
+        m.set_backend_device("CPU")
+    m.set_backend_device("CUDA0")
+    m.set_backend_device(None)
+    a, _ = m.synthesize(np.array([1, 2], np.int32), emb)     # still usable after failed calls
+    assert a.size == 2 * m.samples_per_token()
+    assert m.is_dynamic_global() and m.sample_rate() == 24000
+    assert m.estimate_workspace_bytes(400) > 0
+    m.reserve_workspace(700)
+    assert m.workspace_bytes() > 0
+
+
+def test_f16_linear_mode_is_closer(gguf_paths, emb):
+    """MIO_TTS_B200_LINEAR_DTYPE=f16: fp16 operands for the linears too (10 mantissa bits, like the reference's own
+    TF32 CUDA path).  Run in a subprocess because the mode is read at model load."""
+    path = gguf_paths("default")[0]
+    code = (
+        "import sys, numpy as np; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "from conftest import load_golden, snr_db\n"
+        "from mio_tts_cpp_b200 import MioTTS\n"
+        "z = load_golden('default_T24'); emb = np.load(%r)\n"
+        "m = MioTTS(%r); s = m.decode_spec(z['codes'], emb); a, _ = m.synthesize(z['codes'], emb)\n"
+        "print('SNR', snr_db(s, z['spec']), snr_db(a, z['audio']))\n"
+    ) % (ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "tests", "golden", "en_female_emb.npy"), path)
+    env = dict(os.environ, MIO_TTS_B200_LINEAR_DTYPE="f16")
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = [ln for ln in out.stdout.splitlines() if ln.startswith("SNR")][-1].split()
+    assert float(line[1]) >= 50.0 and float(line[2]) >= 40.0, line
