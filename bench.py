@@ -190,9 +190,9 @@ def run_b200(args, rank, world, local_rank):
                             / peaks["bf16_tflops_sustained"] if world == 1 else None}
         line["stages_ms"] = {k: p[k] for k in ("prenet_ms", "upsample_prior_ms", "decoder_ms", "post_head_ms", "istft_ms",
                                                "total_ms", "attn_ms")}
-        if world == 1:
+        if world == 1 and not args.skip_cpu:
             # ---- CPU baseline: the unmodified reference on this box's host cores, bounded sample ----
-            n_cpu = 6
+            n_cpu = BATCH   # the whole config-2 batch, one utterance after another (~10-30 s of host work)
             v, cores, kind, dt = time_cpu_reference(n_cpu, N_CODES, warmup=1)
             line["cpu_baseline"] = {"value": v, "unit": "audio-seconds/s", "cores": cores, "kind": kind,
                                     "sample": f"{n_cpu} of the 64 utterances x {N_CODES} codes, sequential "
@@ -210,6 +210,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--skip-cpu", action="store_true", help="omit the cpu_baseline leg (profiling runs)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
