@@ -19,6 +19,7 @@
 #include <cuda_fp16.h>
 
 #include <atomic>
+#include <cstdlib>
 #include <mutex>
 
 namespace mio {
@@ -30,15 +31,17 @@ namespace {
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;      // 16-bit elements -> 128-byte rows = one SWIZZLE_128B atom
 constexpr int UMMA_K = 16;
-constexpr int GEMM_THREADS = 192;
+constexpr int EPI_LD = 33;      // padded row of the epilogue transpose tile (conflict-free scalar STS/LDS)
 
-template <int BN> struct tile_cfg {
+template <int BN, int EW> struct tile_cfg {   // EW = epilogue warps per TMEM lane quadrant
+    static constexpr int THREADS = 64 + 128 * EW;
     static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
     static constexpr int B_BYTES = BN * BLOCK_K * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int STAGES = BN == 256 ? 4 : 6;
+    static constexpr int STAGES = BN == 256 ? (EW >= 4 ? 3 : 4) : (EW >= 4 ? 4 : 6);
     static constexpr int TMEM_COLS = 2 * BN;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/ +
+                                      4 * EW * 32 * EPI_LD * 4 /*epilogue transpose tiles*/;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
@@ -126,115 +129,118 @@ __device__ __forceinline__ uint32_t pack16(float a, float b, int dtype) {
 
 __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + __expf(-x)); }
 
-// ---- epilogue of one 32-column chunk held by one thread (row r, columns n .. n+31) ----------------
-template <int EPI>
-__device__ __forceinline__ void epilogue_chunk(const gemm_args & a, int r, int n, uint32_t (&raw)[32]) {
-    float v[32];
-#pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]);
-    const bool full = n + 32 <= a.N;
+// ---- epilogue of one 32x32 accumulator chunk (one warp: TMEM lane quadrant x 32 columns) ----------------
+// tcgen05.ld hands each thread one ROW (32 consecutive columns).  Storing that directly makes every warp-wide
+// access touch 32 different 128-byte lines, so the chunk is first transposed through a padded smem tile
+// (stride 36 floats: conflict-free for both the row-wise STS.128 and the LDS.128 below) and then processed in a
+// coalesced layout: lane -> (row = lane/8 + 4u, 4 consecutive columns), i.e. 4 full 128-byte row segments per
+// warp instruction for the residual / gate / bias loads and the stores.
 
-    if constexpr (EPI == EPI_STORE32) {
-        float * orow = (float *) a.out + (size_t) r * a.ldo + n;
-        const float * gate = a.gate ? a.gate + (size_t) max(a.row_utt[r], 0) * a.gate_ld + n : nullptr;
-        const float * res = a.res ? a.res + (size_t) r * a.ldr + n : nullptr;
-        const bool vec = full && (a.ldo & 3) == 0 && (!res || (a.ldr & 3) == 0);
-        if (vec) {
+// Residual rows of this chunk in the coalesced layout, issued BEFORE the TMEM load so their latency overlaps it.
+__device__ __forceinline__ void epilogue_prefetch(const gemm_args & a, int row0, int lane, int n, float4 (&pre)[8]) {
+    const int col = n + (lane & 7) * 4;
+    const bool ok = a.res != nullptr && (a.ldr & 3) == 0 && col + 4 <= a.N;
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-                float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-                if (a.bias) {
-                    const float4 b = __ldg(reinterpret_cast<const float4 *>(a.bias + n + j));
-                    o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
-                }
-                if (gate) {
-                    const float4 g = __ldg(reinterpret_cast<const float4 *>(gate + j));
-                    o.x *= g.x; o.y *= g.y; o.z *= g.z; o.w *= g.w;
-                }
-                if (res) {
-                    const float4 q = *reinterpret_cast<const float4 *>(res + j);
-                    o.x += q.x; o.y += q.y; o.z += q.z; o.w += q.w;
-                }
-                *reinterpret_cast<float4 *>(orow + j) = o;
-            }
-        } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                if (n + j < a.N) {
-                    float o = v[j];
-                    if (a.bias) o += a.bias[n + j];
-                    if (gate) o *= gate[j];
-                    if (res) o += res[j];
-                    orow[j] = o;
-                }
-            }
-        }
-    } else if constexpr (EPI == EPI_STORE16 || EPI == EPI_ROPE16) {
-        if (a.bias) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) if (n + j < a.N) v[j] += a.bias[n + j];
-        }
-        if constexpr (EPI == EPI_ROPE16) {
-            if (n < a.rope_cols) {   // q and k columns; a 32-column chunk never straddles a head (head_dim % 32 == 0)
-                const int half = a.head_dim >> 1;
-                const float2 * cs = a.rope + (size_t) a.row_pos[r] * half + ((n % a.head_dim) >> 1);
-                const float s = n < a.q_cols ? a.q_scale : 1.0f;
-#pragma unroll
-                for (int i = 0; i < 16; i += 2) {
-                    const float4 c2 = __ldg(reinterpret_cast<const float4 *>(cs + i));   // (cos,sin) x 2
-                    const float x0 = v[2 * i], x1 = v[2 * i + 1], y0 = v[2 * i + 2], y1 = v[2 * i + 3];
-                    v[2 * i]     = (x0 * c2.x - x1 * c2.y) * s;
-                    v[2 * i + 1] = (x0 * c2.y + x1 * c2.x) * s;
-                    v[2 * i + 2] = (y0 * c2.z - y1 * c2.w) * s;
-                    v[2 * i + 3] = (y0 * c2.w + y1 * c2.z) * s;
-                }
-            }
-        }
-        if (full && (a.ldo & 7) == 0) {
-            uint4 * orow = reinterpret_cast<uint4 *>((uint16_t *) a.out + (size_t) r * a.ldo + n);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                uint4 o;
-                o.x = pack16(v[8 * j + 0], v[8 * j + 1], a.out_dtype);
-                o.y = pack16(v[8 * j + 2], v[8 * j + 3], a.out_dtype);
-                o.z = pack16(v[8 * j + 4], v[8 * j + 5], a.out_dtype);
-                o.w = pack16(v[8 * j + 6], v[8 * j + 7], a.out_dtype);
-                orow[j] = o;
-            }
-        } else {
-            uint16_t * orow = (uint16_t *) a.out + (size_t) r * a.ldo + n;
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-                if (n + j < a.N) orow[j] = (uint16_t) (pack16(v[j], 0.0f, a.out_dtype) & 0xFFFF);
-        }
-    } else {   // EPI_SWIGLU16: columns (2j, 2j+1) = (gate_j, up_j)
-        const int no = n >> 1;
-        float h[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) h[j] = silu_f(v[2 * j]) * v[2 * j + 1];
-        if (full && (a.ldo & 7) == 0) {
-            uint4 * orow = reinterpret_cast<uint4 *>((uint16_t *) a.out + (size_t) r * a.ldo + no);
-#pragma unroll
-            for (int j = 0; j < 2; ++j) {
-                uint4 o;
-                o.x = pack16(h[8 * j + 0], h[8 * j + 1], a.out_dtype);
-                o.y = pack16(h[8 * j + 2], h[8 * j + 3], a.out_dtype);
-                o.z = pack16(h[8 * j + 4], h[8 * j + 5], a.out_dtype);
-                o.w = pack16(h[8 * j + 6], h[8 * j + 7], a.out_dtype);
-                orow[j] = o;
-            }
-        } else {
-            uint16_t * orow = (uint16_t *) a.out + (size_t) r * a.ldo + no;
-#pragma unroll
-            for (int j = 0; j < 16; ++j)
-                if (n + 2 * j + 1 < a.N) orow[j] = (uint16_t) (pack16(h[j], 0.0f, a.out_dtype) & 0xFFFF);
-        }
+    for (int u = 0; u < 8; ++u) {
+        const int r = row0 + (lane >> 3) + 4 * u;
+        pre[u] = (ok && r < a.M) ? *reinterpret_cast<const float4 *>(a.res + (size_t) r * a.ldr + col)
+                                 : make_float4(0.f, 0.f, 0.f, 0.f);
     }
 }
 
-template <int BN, int EPI>
-__global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tcgen05_kernel(const __grid_constant__ gemm_args a) {
-    using C = tile_cfg<BN>;
+template <int EPI>
+__device__ __forceinline__ void epilogue_chunk(const gemm_args & a, int row0, int lane, int n, uint32_t (&raw)[32],
+                                               float * stage, const float4 (&pre)[8]) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) stage[lane * EPI_LD + j] = __uint_as_float(raw[j]);
+    __syncwarp();
+    const int c = (lane & 7) * 4;
+    const int col = n + c;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+        const int rr = (lane >> 3) + 4 * u;
+        const int r = row0 + rr;
+        if (r >= a.M || col >= a.N) continue;
+        const float * sp = stage + rr * EPI_LD + c;
+        float x[4] = {sp[0], sp[1], sp[2], sp[3]};
+        const float4 v = make_float4(x[0], x[1], x[2], x[3]);
+        const bool full = col + 4 <= a.N;
+
+        if constexpr (EPI == EPI_STORE32) {
+            float * orow = (float *) a.out + (size_t) r * a.ldo + col;
+            const float * gate = a.gate ? a.gate + (size_t) max(a.row_utt[r], 0) * a.gate_ld + col : nullptr;
+            const float * res = a.res ? a.res + (size_t) r * a.ldr + col : nullptr;
+            if (full && (a.ldo & 3) == 0 && (!res || (a.ldr & 3) == 0)) {
+                float4 o = v;
+                if (a.bias) {
+                    const float4 b = __ldg(reinterpret_cast<const float4 *>(a.bias + col));
+                    o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
+                }
+                if (gate) {
+                    const float4 g = __ldg(reinterpret_cast<const float4 *>(gate));
+                    o.x *= g.x; o.y *= g.y; o.z *= g.z; o.w *= g.w;
+                }
+                if (res) {
+                    const float4 q = pre[u];
+                    o.x += q.x; o.y += q.y; o.z += q.z; o.w += q.w;
+                }
+                *reinterpret_cast<float4 *>(orow) = o;
+            } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    if (col + e < a.N) {
+                        float o = x[e];
+                        if (a.bias) o += a.bias[col + e];
+                        if (gate) o *= gate[e];
+                        if (res) o += res[e];
+                        orow[e] = o;
+                    }
+                }
+            }
+        } else if constexpr (EPI == EPI_STORE16 || EPI == EPI_ROPE16) {
+            if (a.bias) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) if (col + e < a.N) x[e] += a.bias[col + e];
+            }
+            if constexpr (EPI == EPI_ROPE16) {
+                if (col < a.rope_cols) {   // q and k columns; (col, col+1), (col+2, col+3) are rotation pairs
+                    const int half = a.head_dim >> 1;
+                    const float4 cs = __ldg(reinterpret_cast<const float4 *>(
+                        a.rope + (size_t) a.row_pos[r] * half + ((col % a.head_dim) >> 1)));   // (cos,sin) x 2
+                    const float s = col < a.q_cols ? a.q_scale : 1.0f;
+                    const float x0 = x[0], x1 = x[1], y0 = x[2], y1 = x[3];
+                    x[0] = (x0 * cs.x - x1 * cs.y) * s;
+                    x[1] = (x0 * cs.y + x1 * cs.x) * s;
+                    x[2] = (y0 * cs.z - y1 * cs.w) * s;
+                    x[3] = (y0 * cs.w + y1 * cs.z) * s;
+                }
+            }
+            uint16_t * orow = (uint16_t *) a.out + (size_t) r * a.ldo + col;
+            if (full && (a.ldo & 3) == 0) {
+                *reinterpret_cast<uint2 *>(orow) = make_uint2(pack16(x[0], x[1], a.out_dtype), pack16(x[2], x[3], a.out_dtype));
+            } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                    if (col + e < a.N) orow[e] = (uint16_t) (pack16(x[e], 0.0f, a.out_dtype) & 0xFFFF);
+            }
+        } else {   // EPI_SWIGLU16: columns (2j, 2j+1) = (gate_j, up_j); N is even
+            uint16_t * orow = (uint16_t *) a.out + (size_t) r * a.ldo + (col >> 1);
+            const float h0 = silu_f(x[0]) * x[1];
+            const float h1 = silu_f(x[2]) * x[3];
+            if (full && (a.ldo & 1) == 0) {
+                *reinterpret_cast<uint32_t *>(orow) = pack16(h0, h1, a.out_dtype);
+            } else {
+                orow[0] = (uint16_t) (pack16(h0, 0.0f, a.out_dtype) & 0xFFFF);
+                if (col + 3 < a.N) orow[1] = (uint16_t) (pack16(h1, 0.0f, a.out_dtype) & 0xFFFF);
+            }
+        }
+    }
+    __syncwarp();
+}
+
+template <int BN, int EPI, int EW>
+__global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __grid_constant__ gemm_args a) {
+    using C = tile_cfg<BN, EW>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t bar_base = smem_base + C::STAGES * C::STAGE_BYTES;
@@ -258,7 +264,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tcgen05_kernel(const __g
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < C::STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); }
+        for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4 * EW); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -325,6 +331,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tcgen05_kernel(const __g
     } else {
         // ===== epilogue warps =====
         const int quad = warp & 3;                   // TMEM lane quadrant this warp may access
+        const int ew = warp - 2;                     // epilogue warp index; column group = ew / 4
+        const int cgrp = ew >> 2;
+        float * stage = reinterpret_cast<float *>(smem_raw + (bar_base + 256 - smem_u32(smem_raw))) + ew * (32 * EPI_LD);
         uint32_t it = 0;
         for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
             const int m0 = (t / num_n_tiles) * BLOCK_M;
@@ -332,16 +341,18 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tcgen05_kernel(const __g
             const int acc = it & 1;
             mbar_wait(tfull_bar(acc), (it >> 1) & 1);
             tcgen05_fence_after();
-            const int r = m0 + quad * 32 + lane;
+            const int row0 = m0 + quad * 32;
             const uint32_t taddr = tmem_base + ((uint32_t) (quad * 32) << 16) + acc * BN;
 #pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
+            for (int c = cgrp; c < BN / 32; c += EW) {
                 const int n = n0 + c * 32;
                 if (n >= a.N) break;                 // warp-uniform
+                float4 pre[8];
+                if constexpr (EPI == EPI_STORE32) epilogue_prefetch(a, row0, lane, n, pre);
                 uint32_t raw[32];
                 tmem_ld_32x32b_x32(taddr + c * 32, raw);
                 tmem_ld_wait();
-                if (r < a.M) epilogue_chunk<EPI>(a, r, n, raw);
+                if (row0 < a.M) epilogue_chunk<EPI>(a, row0, lane, n, raw, stage, pre);   // warp-uniform
             }
             tcgen05_fence_before();
             __syncwarp();
@@ -378,29 +389,29 @@ encode_tiled_fn get_encode_fn() {
     return fn;
 }
 
-template <int BN, int EPI> void launch_t(const gemm_args & a, int num_sms, cudaStream_t st) {
-    using C = tile_cfg<BN>;
+template <int BN, int EPI, int EW> void launch_t(const gemm_args & a, int num_sms, cudaStream_t st) {
+    using C = tile_cfg<BN, EW>;
     static bool configured[64] = {false};   // per-device function attribute
     int dev = 0;
     MIO_CUDA(cudaGetDevice(&dev));
     if (!configured[dev & 63]) {
-        MIO_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        MIO_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, EPI, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       C::SMEM_BYTES));
         configured[dev & 63] = true;
     }
     const int tiles = ((a.M + BLOCK_M - 1) / BLOCK_M) * ((a.N + BN - 1) / BN);
     const int grid = tiles < num_sms ? tiles : num_sms;
-    gemm_tcgen05_kernel<BN, EPI><<<grid, GEMM_THREADS, C::SMEM_BYTES, st>>>(a);
+    gemm_tcgen05_kernel<BN, EPI, EW><<<grid, C::THREADS, C::SMEM_BYTES, st>>>(a);
     MIO_CUDA(cudaGetLastError());
     count_launch();
 }
 
-template <int BN> void launch_bn(const gemm_args & a, int num_sms, cudaStream_t st) {
+template <int BN, int EW> void launch_bn(const gemm_args & a, int num_sms, cudaStream_t st) {
     switch (a.epilogue) {
-        case EPI_STORE32: launch_t<BN, EPI_STORE32>(a, num_sms, st); break;
-        case EPI_STORE16: launch_t<BN, EPI_STORE16>(a, num_sms, st); break;
-        case EPI_SWIGLU16: launch_t<BN, EPI_SWIGLU16>(a, num_sms, st); break;
-        case EPI_ROPE16: launch_t<BN, EPI_ROPE16>(a, num_sms, st); break;
+        case EPI_STORE32: launch_t<BN, EPI_STORE32, EW>(a, num_sms, st); break;
+        case EPI_STORE16: launch_t<BN, EPI_STORE16, EW>(a, num_sms, st); break;
+        case EPI_SWIGLU16: launch_t<BN, EPI_SWIGLU16, EW>(a, num_sms, st); break;
+        case EPI_ROPE16: launch_t<BN, EPI_ROPE16, EW>(a, num_sms, st); break;
         default: throw cuda_error("gemm: bad epilogue");
     }
 }
@@ -426,8 +437,21 @@ CUtensorMap make_tmap_16(const void * ptr, uint64_t rows, uint64_t cols, uint32_
 void gemm_launch(const gemm_args & a, int num_sms, cudaStream_t st) {
     if (a.M <= 0 || a.N <= 0 || a.K <= 0) return;
     if (a.epilogue == EPI_ROPE16 && (a.head_dim % 32) != 0) throw cuda_error("gemm: rope epilogue needs head_dim % 32 == 0");
-    if (gemm_block_n(a.N) == 256) launch_bn<256>(a, num_sms, st);
-    else launch_bn<128>(a, num_sms, st);
+    static int ew = -1;
+    if (ew < 0) {   // epilogue warps per TMEM quadrant: memory-level parallelism of the residual read-modify-write
+        const char * e = std::getenv("MIO_TTS_B200_GEMM_EW");
+        ew = e ? std::atoi(e) : 4;
+        if (ew != 1 && ew != 2 && ew != 4) ew = 4;
+    }
+    if (gemm_block_n(a.N) == 256) {
+        if (ew == 1) launch_bn<256, 1>(a, num_sms, st);
+        else if (ew == 2) launch_bn<256, 2>(a, num_sms, st);
+        else launch_bn<256, 4>(a, num_sms, st);
+    } else {
+        if (ew == 1) launch_bn<128, 1>(a, num_sms, st);
+        else if (ew == 2) launch_bn<128, 2>(a, num_sms, st);
+        else launch_bn<128, 4>(a, num_sms, st);
+    }
 }
 
 } // namespace mio
