@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <cstdio>
 #include <cstring>
 #include <unordered_map>
 
@@ -394,6 +395,7 @@ void engine::gemm(const dbuf & a, const dev_linear & w, int M, int epilogue, voi
     if (prof_gemm_) {
         MIO_CUDA(cudaEventRecord(gemm_ev_[evi + 1], st_));
         gemm_ev_flops_.push_back({evi, 2.0 * (double) (lay ? lay->valid : M) * w.N * w.K * w.taps});
+        gemm_ev_shape_.push_back({M, w.N, w.K, w.taps, epilogue});
     }
 }
 
@@ -454,6 +456,7 @@ void engine::run(bool with_istft, stage_times * prof, int stop_stage) {
     prof_ = prof;
     prof_gemm_ = prof != nullptr;
     gemm_ev_flops_.clear();
+    gemm_ev_shape_.clear();
     attn_ev_.clear();
     const int pd = hp.prenet_dim, dd = hp.decoder_dim;
     const int ldt = mdl->linear_dtype;
@@ -551,9 +554,16 @@ void engine::run(bool with_istft, stage_times * prof, int stop_stage) {
         prof->prenet = ms(0, 1); prof->upsample_prior = ms(1, 2); prof->decoder = ms(2, 3);
         prof->post_head = ms(3, 4); prof->istft = ms(4, 5); prof->total = ms(0, 5);
         prof->gemm_ms = 0; prof->gemm_flops = 0; prof->gemm_launches = (int) gemm_ev_flops_.size();
-        for (auto & ef : gemm_ev_flops_) {
+        const bool log = std::getenv("MIO_TTS_B200_GEMM_LOG") != nullptr;
+        for (size_t gi = 0; gi < gemm_ev_flops_.size(); ++gi) {
+            auto & ef = gemm_ev_flops_[gi];
             float t = 0;
             cudaEventElapsedTime(&t, gemm_ev_[ef.first], gemm_ev_[ef.first + 1]);
+            if (log) {
+                const auto & sh = gemm_ev_shape_[gi];
+                std::fprintf(stderr, "gemm M=%d N=%d K=%d taps=%d epi=%d  %.1f us  %.0f TFLOP/s\n", sh[0], sh[1], sh[2],
+                             sh[3], sh[4], t * 1e3, ef.second / (t * 1e-3) / 1e12);
+            }
             prof->gemm_ms += t;
             prof->gemm_flops += ef.second;
         }

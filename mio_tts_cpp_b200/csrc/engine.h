@@ -8,6 +8,7 @@
 #pragma once
 #include "model.h"
 
+#include <array>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -80,6 +81,7 @@ private:
     stage_times * prof_ = nullptr;
     std::vector<std::pair<size_t, double>> gemm_ev_flops_;   // (event pair index, flops)
     std::vector<size_t> attn_ev_;
+    std::vector<std::array<int, 5>> gemm_ev_shape_;   // M, N, K, taps, epilogue
 
     // batch state
     int n_utt_ = 0;

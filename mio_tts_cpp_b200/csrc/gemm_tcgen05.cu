@@ -136,21 +136,34 @@ __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + __expf(-x)
 // coalesced layout: lane -> (row = lane/8 + 4u, 4 consecutive columns), i.e. 4 full 128-byte row segments per
 // warp instruction for the residual / gate / bias loads and the stores.
 
-// Residual rows of this chunk in the coalesced layout, issued BEFORE the TMEM load so their latency overlaps it.
-__device__ __forceinline__ void epilogue_prefetch(const gemm_args & a, int row0, int lane, int n, float4 (&pre)[8]) {
+// Per-chunk operands in the coalesced layout, issued BEFORE the TMEM load so their latency overlaps it:
+// the residual rows (EPI_STORE32) or the RoPE (cos,sin) pairs of the rows' positions (EPI_ROPE16).
+// rmeta[u] = utterance (gate) or position (rope) of unit row u, loaded once per tile.
+template <int EPI>
+__device__ __forceinline__ void epilogue_prefetch(const gemm_args & a, int row0, int lane, int n, const int (&rmeta)[8],
+                                                  float4 (&pre)[8]) {
     const int col = n + (lane & 7) * 4;
-    const bool ok = a.res != nullptr && (a.ldr & 3) == 0 && col + 4 <= a.N;
+    if constexpr (EPI == EPI_STORE32) {
+        const bool ok = a.res != nullptr && (a.ldr & 3) == 0 && col + 4 <= a.N;
 #pragma unroll
-    for (int u = 0; u < 8; ++u) {
-        const int r = row0 + (lane >> 3) + 4 * u;
-        pre[u] = (ok && r < a.M) ? *reinterpret_cast<const float4 *>(a.res + (size_t) r * a.ldr + col)
-                                 : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int u = 0; u < 8; ++u) {
+            const int r = row0 + (lane >> 3) + 4 * u;
+            pre[u] = (ok && r < a.M) ? *reinterpret_cast<const float4 *>(a.res + (size_t) r * a.ldr + col)
+                                     : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    } else if constexpr (EPI == EPI_ROPE16) {
+        const int half = a.head_dim >> 1;
+        const int pair = (col % a.head_dim) >> 1;
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+            pre[u] = col < a.rope_cols ? __ldg(reinterpret_cast<const float4 *>(a.rope + (size_t) rmeta[u] * half + pair))
+                                       : make_float4(1.f, 0.f, 1.f, 0.f);
     }
 }
 
 template <int EPI>
 __device__ __forceinline__ void epilogue_chunk(const gemm_args & a, int row0, int lane, int n, uint32_t (&raw)[32],
-                                               float * stage, const float4 (&pre)[8]) {
+                                               float * stage, const int (&rmeta)[8], const float4 (&pre)[8]) {
 #pragma unroll
     for (int j = 0; j < 32; ++j) stage[lane * EPI_LD + j] = __uint_as_float(raw[j]);
     __syncwarp();
@@ -168,7 +181,7 @@ __device__ __forceinline__ void epilogue_chunk(const gemm_args & a, int row0, in
 
         if constexpr (EPI == EPI_STORE32) {
             float * orow = (float *) a.out + (size_t) r * a.ldo + col;
-            const float * gate = a.gate ? a.gate + (size_t) max(a.row_utt[r], 0) * a.gate_ld + col : nullptr;
+            const float * gate = a.gate ? a.gate + (size_t) max(rmeta[u], 0) * a.gate_ld + col : nullptr;
             const float * res = a.res ? a.res + (size_t) r * a.ldr + col : nullptr;
             if (full && (a.ldo & 3) == 0 && (!res || (a.ldr & 3) == 0)) {
                 float4 o = v;
@@ -204,9 +217,7 @@ __device__ __forceinline__ void epilogue_chunk(const gemm_args & a, int row0, in
             }
             if constexpr (EPI == EPI_ROPE16) {
                 if (col < a.rope_cols) {   // q and k columns; (col, col+1), (col+2, col+3) are rotation pairs
-                    const int half = a.head_dim >> 1;
-                    const float4 cs = __ldg(reinterpret_cast<const float4 *>(
-                        a.rope + (size_t) a.row_pos[r] * half + ((col % a.head_dim) >> 1)));   // (cos,sin) x 2
+                    const float4 cs = pre[u];   // (cos,sin) x 2
                     const float s = col < a.q_cols ? a.q_scale : 1.0f;
                     const float x0 = x[0], x1 = x[1], y0 = x[2], y1 = x[3];
                     x[0] = (x0 * cs.x - x1 * cs.y) * s;
@@ -339,20 +350,29 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
             const int m0 = (t / num_n_tiles) * BLOCK_M;
             const int n0 = (t % num_n_tiles) * BN;
             const int acc = it & 1;
+            const int row0 = m0 + quad * 32;
+            int rmeta[8];
+            {
+                const int * mp = EPI == EPI_ROPE16 ? a.row_pos : (EPI == EPI_STORE32 && a.gate ? a.row_utt : nullptr);
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int r = row0 + (lane >> 3) + 4 * u;
+                    rmeta[u] = (mp != nullptr && r < a.M) ? __ldg(mp + r) : 0;
+                }
+            }
+            const uint32_t taddr = tmem_base + ((uint32_t) (quad * 32) << 16) + acc * BN;
             mbar_wait(tfull_bar(acc), (it >> 1) & 1);
             tcgen05_fence_after();
-            const int row0 = m0 + quad * 32;
-            const uint32_t taddr = tmem_base + ((uint32_t) (quad * 32) << 16) + acc * BN;
 #pragma unroll 1
             for (int c = cgrp; c < BN / 32; c += EW) {
                 const int n = n0 + c * 32;
                 if (n >= a.N) break;                 // warp-uniform
                 float4 pre[8];
-                if constexpr (EPI == EPI_STORE32) epilogue_prefetch(a, row0, lane, n, pre);
+                epilogue_prefetch<EPI>(a, row0, lane, n, rmeta, pre);
                 uint32_t raw[32];
                 tmem_ld_32x32b_x32(taddr + c * 32, raw);
                 tmem_ld_wait();
-                if (row0 < a.M) epilogue_chunk<EPI>(a, row0, lane, n, raw, stage, pre);   // warp-uniform
+                if (row0 < a.M) epilogue_chunk<EPI>(a, row0, lane, n, raw, stage, rmeta, pre);   // warp-uniform
             }
             tcgen05_fence_before();
             __syncwarp();
