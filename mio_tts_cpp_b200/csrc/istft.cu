@@ -17,6 +17,7 @@
 #include "common.h"
 
 #include <cmath>
+#include <cstdlib>
 #include <vector>
 
 namespace mio {
@@ -381,10 +382,17 @@ void istft_plan_free(istft_plan & p) {
     p = istft_plan();
 }
 
+bool launch_istft_fast(const istft_plan & p, const float * spec, int pitch, const int * spec_row0, const int * n_frames,
+                       const long long * audio_off, float * audio, unsigned int * peak_bits, int n_utt, int max_frames,
+                       cudaStream_t st);
+
 void launch_istft(const istft_plan & p, const float * spec, int pitch, const int * spec_row0, const int * n_frames,
                   const long long * audio_off, float * audio, unsigned int * peak_bits, int n_utt, int max_frames,
                   cudaStream_t st) {
     if (n_utt <= 0 || max_frames <= 0) return;
+    static const bool no_fast = std::getenv("MIO_TTS_B200_ISTFT_GENERIC") != nullptr;
+    if (!no_fast && launch_istft_fast(p, spec, pitch, spec_row0, n_frames, audio_off, audio, peak_bits, n_utt, max_frames, st))
+        return;
     istft_params P;
     P.n_fft = p.n_fft; P.hop = p.hop; P.M = p.n_fft / 2; P.n_freq = p.n_fft / 2 + 1;
     P.pad = (p.n_fft - p.hop) / 2;
