@@ -57,25 +57,28 @@ __global__ void __launch_bounds__(128) attention_band_kernel(const uint16_t * __
     const int ld = 3 * dim;
     const int kpos0 = t.pos0 - 32;     // position of key index 0
 
-    // ---- stage Q, K, V tiles (16-byte chunks; rows outside the utterance are zero) ----
+    // ---- stage Q, K, V tiles with cp.async (16-byte chunks in flight together; rows outside the utterance are
+    //      zero-filled through src-size 0) ----
+    auto cp16 = [](uint16_t * dst, const uint16_t * src, bool valid) {
+        const uint32_t d = (uint32_t) __cvta_generic_to_shared(dst);
+        const int n = valid ? 16 : 0;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(n) : "memory");
+    };
     for (int c = threadIdx.x; c < TQ * 8; c += blockDim.x) {
         const int i = c >> 3, ch = c & 7;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (i < t.n) v = *reinterpret_cast<const uint4 *>(qkv + (size_t) (t.row0 + i) * ld + head * HD + ch * 8);
-        *reinterpret_cast<uint4 *>(Qs + i * LDS + ch * 8) = v;
+        const bool ok = i < t.n;
+        cp16(Qs + i * LDS + ch * 8, qkv + (size_t) (t.row0 + (ok ? i : 0)) * ld + head * HD + ch * 8, ok);
     }
     for (int c = threadIdx.x; c < TK * 8; c += blockDim.x) {
         const int j = c >> 3, ch = c & 7;
         const int pos = kpos0 + j;
-        uint4 kv = make_uint4(0, 0, 0, 0), vv = make_uint4(0, 0, 0, 0);
-        if (pos >= 0 && pos < t.utt_len) {
-            const uint16_t * p = qkv + (size_t) (t.utt_row0 + pos) * ld + head * HD + ch * 8;
-            kv = *reinterpret_cast<const uint4 *>(p + dim);
-            vv = *reinterpret_cast<const uint4 *>(p + 2 * dim);
-        }
-        *reinterpret_cast<uint4 *>(Ks + j * LDS + ch * 8) = kv;
-        *reinterpret_cast<uint4 *>(Vs + j * LDS + ch * 8) = vv;
+        const bool ok = pos >= 0 && pos < t.utt_len;
+        const uint16_t * p = qkv + (size_t) (t.utt_row0 + (ok ? pos : 0)) * ld + head * HD + ch * 8;
+        cp16(Ks + j * LDS + ch * 8, p + dim, ok);
+        cp16(Vs + j * LDS + ch * 8, p + 2 * dim, ok);
     }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;

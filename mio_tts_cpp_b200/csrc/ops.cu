@@ -241,6 +241,50 @@ __global__ void gn_apply_kernel(const float * __restrict__ x, int rows, int dim,
     reinterpret_cast<uint2 *>(out16)[i] = o;
 }
 
+// fast path: channels-per-group % 4 == 0 (one statistics lookup per float4) and 256 % (dim/4) == 0, so a thread keeps
+// its channel quad (affine weights in registers) and walks rows; SiLU on the SFU (output is rounded to fp16 anyway)
+template <int ROWS_PER_THREAD>
+__global__ void gn_apply_fast_kernel(const float * __restrict__ x, int rows, int dim, int groups,
+                                     const float2 * __restrict__ mr, const float * __restrict__ w,
+                                     const float * __restrict__ b, const int * __restrict__ row_utt, void * out16,
+                                     int out_dtype) {
+    const int c4n = dim >> 2;
+    const int rpb = blockDim.x / c4n;                 // rows per block pass
+    const int c4 = threadIdx.x % c4n;
+    const int g = (c4 * 4) / (dim / groups);
+    const float4 ww = __ldg(reinterpret_cast<const float4 *>(w) + c4);
+    const float4 bb = __ldg(reinterpret_cast<const float4 *>(b) + c4);
+    const int row_base = blockIdx.x * rpb * ROWS_PER_THREAD + threadIdx.x / c4n;
+    float4 v[ROWS_PER_THREAD];
+    int utt[ROWS_PER_THREAD];
+#pragma unroll
+    for (int it = 0; it < ROWS_PER_THREAD; ++it) {
+        const int row = row_base + it * rpb;
+        utt[it] = row < rows ? __ldg(row_utt + row) : -1;
+        if (utt[it] >= 0) v[it] = reinterpret_cast<const float4 *>(x)[(size_t) row * c4n + c4];
+    }
+#pragma unroll
+    for (int it = 0; it < ROWS_PER_THREAD; ++it) {
+        const int row = row_base + it * rpb;
+        if (row >= rows) continue;
+        uint2 o = make_uint2(0u, 0u);
+        if (utt[it] >= 0) {
+            const float2 m = __ldg(mr + (size_t) utt[it] * groups + g);
+            float y[4] = {v[it].x, v[it].y, v[it].z, v[it].w};
+            const float wv[4] = {ww.x, ww.y, ww.z, ww.w};
+            const float bv[4] = {bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float t = ((y[k] - m.x) * m.y) * wv[k] + bv[k];
+                y[k] = __fdividef(t, 1.0f + __expf(-t));
+            }
+            o.x = pack16(y[0], y[1], out_dtype);
+            o.y = pack16(y[2], y[3], out_dtype);
+        }
+        reinterpret_cast<uint2 *>(out16)[(size_t) row * c4n + c4] = o;
+    }
+}
+
 // ---- ggml_interpolate(BILINEAR) along frames only: half-pixel centres, clamped taps
 //      (ggml-cpu/ops.cpp:7577-7617, call src/miocodec-decoder.cpp:1373); identity when lengths match. ----
 __global__ void interp_kernel(const float * __restrict__ src, const int * __restrict__ src_row0,
@@ -402,8 +446,16 @@ void launch_gn_apply(const float * x, int rows, int dim, int groups, const float
                      const float * b, const int * row_utt, void * out16, int out_dtype, cudaStream_t st) {
     if (rows <= 0) return;
     if (dim & 3) throw cuda_error("group norm: channel count must be a multiple of 4");
-    gn_apply_kernel<<<blocks_for((size_t) rows * (dim >> 2), 256), 256, 0, st>>>(
-        x, rows, dim, groups, mean_rstd, w, b, row_utt, out16, out_dtype);
+    const int c4n = dim >> 2, cpg = dim / groups;
+    if ((cpg & 3) == 0 && c4n <= 256 && (256 % c4n) == 0) {
+        constexpr int RPT = 4;
+        const int rows_per_block = (256 / c4n) * RPT;
+        gn_apply_fast_kernel<RPT><<<blocks_for((size_t) rows, rows_per_block), 256, 0, st>>>(
+            x, rows, dim, groups, mean_rstd, w, b, row_utt, out16, out_dtype);
+    } else {
+        gn_apply_kernel<<<blocks_for((size_t) rows * (dim >> 2), 256), 256, 0, st>>>(
+            x, rows, dim, groups, mean_rstd, w, b, row_utt, out16, out_dtype);
+    }
     MIO_CUDA(cudaGetLastError());
     count_launch();
 }
