@@ -54,14 +54,15 @@ enum gemm_epilogue : int {
 
 struct gemm_args {
     CUtensorMap map_a;       // A: [rows, K] 16-bit, box 64 x 128, swizzle 128B
-    CUtensorMap map_b;       // W: [N, taps*K] 16-bit, box 64 x BLOCK_N, swizzle 128B
+    CUtensorMap map_b;       // W: [N, taps*K] 16-bit, box 64 x gemm_w_box_rows(), swizzle 128B
+    CUtensorMap map_out;     // output (and in-place residual): box 32 x 32, swizzle 128B (fp32) / 64B (16-bit)
     int M, N, K, taps;
     int dtype;               // op16 of A and W
     int out_dtype;           // op16 of a 16-bit output
     int epilogue;
     void * out; int ldo;
     const float * bias;
-    const float * res; int ldr;
+    const float * res; int ldr;          // fp32 residual: nullptr or == out (read through map_out)
     const float * gate; int gate_ld;     // gate[utt * gate_ld + n]
     const int * row_utt;                 // row -> utterance (needed with gate)
     const int * row_pos;                 // row -> position in utterance (needed with rope)
@@ -72,7 +73,10 @@ struct gemm_args {
 void gemm_launch(const gemm_args & a, int num_sms, cudaStream_t st);
 // A-operand / weight tensor maps (row-major [rows, cols] 16-bit, cols contiguous)
 CUtensorMap make_tmap_16(const void * ptr, uint64_t rows, uint64_t cols, uint32_t box_rows);
-int gemm_block_n(int N);   // tile width the launcher will use for this N (weights' map box must match)
+// output tensor map: [rows, cols] of 2- or 4-byte elements, row pitch ld_elems (stores clip to rows x cols)
+CUtensorMap make_tmap_out(const void * ptr, uint64_t rows, uint64_t cols, uint64_t ld_elems, int elem_bytes);
+int gemm_block_n(int N);   // tile width the launcher will use for this N (weight rows are padded to it)
+int gemm_w_box_rows();      // rows per TMA box of a weight tensor map
 
 // ---------------------------------------------------------------------------------------------
 // elementwise / normalisation kernels (ops.cu)

@@ -104,7 +104,8 @@ void engine::ensure(dbuf & b, size_t bytes) {
     MIO_CUDA(cudaMalloc(&b.p, cap));
     MIO_CUDA(cudaMemsetAsync(b.p, 0, cap, st_));
     b.cap = cap;
-    tmaps_.clear();   // cached A-operand tensor maps may point at the freed buffer
+    tmaps_.clear();   // cached tensor maps may point at the freed buffer
+    omaps_.clear();
 }
 
 size_t engine::workspace_bytes() const {
@@ -139,6 +140,16 @@ const CUtensorMap & engine::amap(const dbuf & b, int K) {
     if (it != tmaps_.end()) return it->second;
     const uint64_t rows = b.cap / ((size_t) K * 2);
     auto ins = tmaps_.emplace(key, make_tmap_16(b.p, rows, (uint64_t) K, 128));
+    return ins.first->second;
+}
+
+const CUtensorMap & engine::omap(const void * p, int rows, int cols, int ld, int elem_bytes) {
+    const std::array<uint64_t, 5> key = {(uint64_t) (uintptr_t) p, (uint64_t) rows, (uint64_t) cols, (uint64_t) ld,
+                                         (uint64_t) elem_bytes};
+    auto it = omaps_.find(key);
+    if (it != omaps_.end()) return it->second;
+    if (omaps_.size() > 512) omaps_.clear();   // batches of many different shapes: bound the cache
+    auto ins = omaps_.emplace(key, make_tmap_out(p, (uint64_t) rows, (uint64_t) cols, (uint64_t) ld, elem_bytes));
     return ins.first->second;
 }
 
@@ -374,6 +385,7 @@ void engine::gemm(const dbuf & a, const dev_linear & w, int M, int epilogue, voi
     std::memset(&g, 0, sizeof(g));
     g.map_a = amap(a, w.K);
     g.map_b = w.map_b;
+    g.map_out = omap(out, M, epilogue == EPI_SWIGLU16 ? w.N / 2 : w.N, ldo, epilogue == EPI_STORE32 ? 4 : 2);
     g.M = M; g.N = w.N; g.K = w.K; g.taps = w.taps;
     g.dtype = w.dtype; g.out_dtype = out_dtype; g.epilogue = epilogue;
     g.out = out; g.ldo = ldo; g.bias = bias; g.res = res; g.ldr = ldr;

@@ -106,11 +106,13 @@ private:
     const void * dbg_ptr_ = nullptr; int dbg_cols_ = 0, dbg_is16_ = 0, dbg_dtype_ = 0; const seq_layout * dbg_lay_ = nullptr;
     float2 * rope_p_ = nullptr, * rope_d_ = nullptr; int rope_p_pos_ = 0, rope_d_pos_ = 0;
     std::map<std::pair<const void *, int>, CUtensorMap> tmaps_;
+    std::map<std::array<uint64_t, 5>, CUtensorMap> omaps_;   // (ptr, rows, cols, ld, elem bytes) -> output map
     std::map<std::pair<int, int>, istft_plan> istft_plans_;
 
     void ensure(dbuf & b, size_t bytes);
     void ensure_rope(int prenet_pos, int decoder_pos);
     const CUtensorMap & amap(const dbuf & b, int K);
+    const CUtensorMap & omap(const void * p, int rows, int cols, int ld, int elem_bytes);
     void build_layout(seq_layout & L, const std::vector<int> & len, int gap);
     void append_layout(seq_layout & L);
     void bind_layout(seq_layout & L);

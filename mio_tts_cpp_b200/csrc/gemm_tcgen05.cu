@@ -7,12 +7,22 @@
 // taps = 3: ggml_conv_1d_ph k=3 of resnet_block_eval (:1293-1330) as an implicit GEMM: three row-shifted TMA
 //           loads of the same [rows, C] activation; zero gap rows of the row layout give the "same" padding.
 //
-// Structure (one persistent CTA per SM, 192 threads):
+// Two SMs of a TPC work as a CTA pair (cluster 2x1x1, tcgen05 cta_group::2) on one 256 x BLOCK_N tile: each CTA
+// stages its own 128 rows of A and HALF of the W tile, the leader's single MMA thread drives both tensor cores
+// (UMMA M=256), and each CTA keeps the accumulator of its 128 rows in its own TMEM.  Per-SM L2->smem traffic per
+// FLOP drops by a third against the 128 x 256 single-CTA tile and one more pipeline stage fits.
+// (NCTA=1 keeps the single-CTA form for BLOCK_N=128 and for A/B testing: MIO_TTS_B200_GEMM_CTA=1.)
+//
+// Structure (one persistent CTA per SM):
 //   warp 0      TMA producer: cp.async.bulk.tensor.2d -> 128B-swizzled smem stages, mbarrier complete_tx
 //   warp 1      allocates TMEM; one lane issues tcgen05.mma.cta_group::1.kind::f16 (M=128, N=BLOCK_N, K=16),
 //               tcgen05.commit releases smem stages / publishes the accumulator
-//   warps 2..5  epilogue: tcgen05.ld 32x32b.x32 -> registers -> fused bias / gate / residual / SwiGLU / RoPE
-//               -> vectorised global stores.  Two TMEM accumulator buffers overlap epilogue(i) with MMA(i+1).
+//   warps 2..   epilogue (4*EW warps; a warp may only touch TMEM lanes 32*(warp%4)..+31): per 32-row x 32/64-column
+//               chunk tcgen05.ld 32x32b.x32 hands each thread one ROW; the fused bias / AdaLN gate / residual /
+//               SwiGLU / RoPE math runs in that layout, the result goes to a swizzled smem box and ONE lane issues a
+//               TMA store (cp.async.bulk.tensor .global.shared::cta), so output rows are written as full 64/128-byte
+//               lines without per-thread address arithmetic.  The fp32 residual (always the in-place output) is
+//               TMA-LOADED into the same box two chunks ahead.  Two TMEM accumulators overlap epilogue(i) with MMA(i+1).
 #include "common.h"
 
 #include <cuda_bf16.h>
@@ -20,6 +30,7 @@
 
 #include <atomic>
 #include <cstdlib>
+#include <cstring>
 #include <mutex>
 
 namespace mio {
@@ -31,17 +42,35 @@ namespace {
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;      // 16-bit elements -> 128-byte rows = one SWIZZLE_128B atom
 constexpr int UMMA_K = 16;
-constexpr int EPI_LD = 33;      // padded row of the epilogue transpose tile (conflict-free scalar STS/LDS)
+constexpr int B_BOX_ROWS = 128;  // rows of W per TMA box (a BLOCK_N=256 single-CTA stage takes two boxes)
+constexpr uint32_t PEER_BIT_MASK = 0xFEFFFFFFu;   // clears the CTA-pair rank bit of a shared::cluster address
+constexpr int EPI_NBUF = 3;      // output boxes per epilogue warp (residual prefetch distance = 2 chunks)
 
-template <int BN, int EW> struct tile_cfg {   // EW = epilogue warps per TMEM lane quadrant
+// per-epilogue chunk geometry: CW accumulator columns -> one 32-row box of ROW_BYTES per row
+template <int EPI> struct epi_cfg {
+    static constexpr int CW = EPI == EPI_SWIGLU16 ? 64 : 32;
+    static constexpr int ROW_BYTES = EPI == EPI_STORE32 ? 128 : 64;
+    static constexpr int BUF_BYTES = 32 * ROW_BYTES;
+    static constexpr int ROPE_BYTES = EPI == EPI_ROPE16 ? 4096 : 0;      // (cos,sin) rows of the chunk, transposed
+    static constexpr int WARP_BYTES = EPI_NBUF * BUF_BYTES + ROPE_BYTES;
+};
+
+template <int BN, int EPI, int EW, int NCTA> struct tile_cfg {   // EW = epilogue warps per TMEM lane quadrant
     static constexpr int THREADS = 64 + 128 * EW;
     static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
-    static constexpr int B_BYTES = BN * BLOCK_K * 2;
+    static constexpr int B_ROWS = BN / NCTA;               // rows of the W tile staged by ONE CTA
+    static constexpr int B_BYTES = B_ROWS * BLOCK_K * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int STAGES = BN == 256 ? (EW >= 4 ? 3 : 4) : (EW >= 4 ? 4 : 6);
+    static constexpr int EPI_BYTES = 4 * EW * epi_cfg<EPI>::WARP_BYTES;
+    static constexpr int BAR_BYTES = 768;                  // pipeline barriers [0,256) + per-warp residual barriers
+    static constexpr int STAGES_FIT = (227 * 1024 - 1024 - BAR_BYTES - EPI_BYTES) / STAGE_BYTES;
+    static constexpr int STAGES = STAGES_FIT > 8 ? 8 : STAGES_FIT;
     static constexpr int TMEM_COLS = 2 * BN;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/ +
-                                      4 * EW * 32 * EPI_LD * 4 /*epilogue transpose tiles*/;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + EPI_BYTES + BAR_BYTES;
+    static_assert(B_ROWS % B_BOX_ROWS == 0, "W stage must be a whole number of TMA boxes");
+    static_assert(2 * STAGES + 5 <= 32, "pipeline barrier block is 256 bytes");
+    static_assert(256 + 4 * EW * EPI_NBUF * 8 <= BAR_BYTES, "residual barrier block");
+    static_assert(STAGES >= 2, "not enough shared memory for the operand pipeline");
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
@@ -78,19 +107,76 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap * ma
         ::"r"(dst), "l"((uint64_t) map), "r"(bar), "r"(c0), "r"(c1)
         : "memory");
 }
+// CTA-pair forms: the load lands in the issuing CTA's smem, its bytes are counted on the LEADER's mbarrier
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap * map, uint32_t bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"((uint64_t) map), "r"(bar & PEER_BIT_MASK), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar & PEER_BIT_MASK) : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap * map, uint32_t src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"((uint64_t) map), "r"(src), "r"(c0), "r"(c1)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void bulk_wait_read() {   // smem of all but the N newest stores is reusable
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, float4 v) {
+    asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void sts128u(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
 __device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tcgen05_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+template <int NCTA> __device__ __forceinline__ void tcgen05_commit(uint32_t bar) {
+    if constexpr (NCTA == 1) {
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+    } else {   // arrives on the barrier at this offset in BOTH CTAs of the pair
+        asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                     ::"r"(bar), "h"((uint16_t) 3)
+                     : "memory");
+    }
 }
+template <int NCTA>
 __device__ __forceinline__ void tcgen05_mma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
                                                 uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
-        : "memory");
+    if constexpr (NCTA == 1) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "setp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+            ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+            : "memory");
+    } else {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "setp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+            ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+            : "memory");
+    }
 }
 __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile(
@@ -127,135 +213,104 @@ __device__ __forceinline__ uint32_t pack16(float a, float b, int dtype) {
     return *reinterpret_cast<uint32_t *>(&v);
 }
 
-__device__ __forceinline__ float silu_f(float x) { return x / (1.0f + __expf(-x)); }
+// x * sigmoid(x) on the SFU (ex2.approx + rcp.approx, ~2 ulp; the result is rounded to 16 bits anyway)
+__device__ __forceinline__ float silu_f(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
 
-// ---- epilogue of one 32x32 accumulator chunk (one warp: TMEM lane quadrant x 32 columns) ----------------
-// tcgen05.ld hands each thread one ROW (32 consecutive columns).  Storing that directly makes every warp-wide
-// access touch 32 different 128-byte lines, so the chunk is first transposed through a padded smem tile
-// (stride 36 floats: conflict-free for both the row-wise STS.128 and the LDS.128 below) and then processed in a
-// coalesced layout: lane -> (row = lane/8 + 4u, 4 consecutive columns), i.e. 4 full 128-byte row segments per
-// warp instruction for the residual / gate / bias loads and the stores.
+// ---- epilogue math of one chunk, row-per-thread (tcgen05.ld 32x32b: lane = row, 32 consecutive columns) ----------
+// Output boxes in shared memory use the TMA swizzle of their tensor map so that a quarter-warp's 16-byte accesses
+// hit 32 distinct banks: SWIZZLE_128B for 128-byte rows (fp32), SWIZZLE_64B for 64-byte rows (16-bit).
 
-// Per-chunk operands in the coalesced layout, issued BEFORE the TMEM load so their latency overlaps it:
-// the residual rows (EPI_STORE32) or the RoPE (cos,sin) pairs of the rows' positions (EPI_ROPE16).
-// rmeta[u] = utterance (gate) or position (rope) of unit row u, loaded once per tile.
-template <int EPI>
-__device__ __forceinline__ void epilogue_prefetch(const gemm_args & a, int row0, int lane, int n, const int (&rmeta)[8],
-                                                  float4 (&pre)[8]) {
-    const int col = n + (lane & 7) * 4;
-    if constexpr (EPI == EPI_STORE32) {
-        const bool ok = a.res != nullptr && (a.ldr & 3) == 0 && col + 4 <= a.N;
+// fp32 box: out = (acc + bias) * gate + residual, residual read from / result written to the same box slot
+__device__ __forceinline__ void chunk_store32(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, int lane, int n,
+                                              int utt, bool has_res) {
+    const uint32_t row = buf + lane * 128;
+    const uint32_t sw = (uint32_t) (lane & 7) << 4;
+    const float * gate = a.gate ? a.gate + (size_t) utt * a.gate_ld + n : nullptr;
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            const int r = row0 + (lane >> 3) + 4 * u;
-            pre[u] = (ok && r < a.M) ? *reinterpret_cast<const float4 *>(a.res + (size_t) r * a.ldr + col)
-                                     : make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int j = 0; j < 8; ++j) {
+        const uint32_t addr = row + (((uint32_t) j << 4) ^ sw);
+        float4 o = make_float4(__uint_as_float(raw[4 * j]), __uint_as_float(raw[4 * j + 1]), __uint_as_float(raw[4 * j + 2]),
+                               __uint_as_float(raw[4 * j + 3]));
+        const bool in = n + 4 * j < a.N;      // columns past N are clipped by the TMA store; do not read past the vectors
+        if (a.bias && in) {
+            const float4 b = __ldg(reinterpret_cast<const float4 *>(a.bias + n) + j);
+            o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
         }
-    } else if constexpr (EPI == EPI_ROPE16) {
-        const int half = a.head_dim >> 1;
-        const int pair = (col % a.head_dim) >> 1;
-#pragma unroll
-        for (int u = 0; u < 8; ++u)
-            pre[u] = col < a.rope_cols ? __ldg(reinterpret_cast<const float4 *>(a.rope + (size_t) rmeta[u] * half + pair))
-                                       : make_float4(1.f, 0.f, 1.f, 0.f);
+        if (gate && in) {
+            const float4 g = __ldg(reinterpret_cast<const float4 *>(gate) + j);
+            o.x *= g.x; o.y *= g.y; o.z *= g.z; o.w *= g.w;
+        }
+        if (has_res) {
+            const float4 q = lds128(addr);
+            o.x += q.x; o.y += q.y; o.z += q.z; o.w += q.w;
+        }
+        sts128(addr, o);
     }
 }
 
-template <int EPI>
-__device__ __forceinline__ void epilogue_chunk(const gemm_args & a, int row0, int lane, int n, uint32_t (&raw)[32],
-                                               float * stage, const int (&rmeta)[8], const float4 (&pre)[8]) {
+// 16-bit box of 32 columns (+ bias); RoPE on (even, odd) column pairs with this row's (cos, sin) from the staging tile
+template <bool ROPE>
+__device__ __forceinline__ void chunk_store16(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, uint32_t rope_st,
+                                              int lane, int n, bool rotate, float scale) {
+    const uint32_t row = buf + lane * 64;
+    const uint32_t sw = (uint32_t) ((lane >> 1) & 3) << 4;
+    const uint32_t rrow = rope_st + lane * 128;
+    const uint32_t rsw = (uint32_t) (lane & 7) << 4;
 #pragma unroll
-    for (int j = 0; j < 32; ++j) stage[lane * EPI_LD + j] = __uint_as_float(raw[j]);
-    __syncwarp();
-    const int c = (lane & 7) * 4;
-    const int col = n + c;
+    for (int j = 0; j < 4; ++j) {
+        float x[8];
 #pragma unroll
-    for (int u = 0; u < 8; ++u) {
-        const int rr = (lane >> 3) + 4 * u;
-        const int r = row0 + rr;
-        if (r >= a.M || col >= a.N) continue;
-        const float * sp = stage + rr * EPI_LD + c;
-        float x[4] = {sp[0], sp[1], sp[2], sp[3]};
-        const float4 v = make_float4(x[0], x[1], x[2], x[3]);
-        const bool full = col + 4 <= a.N;
-
-        if constexpr (EPI == EPI_STORE32) {
-            float * orow = (float *) a.out + (size_t) r * a.ldo + col;
-            const float * gate = a.gate ? a.gate + (size_t) max(rmeta[u], 0) * a.gate_ld + col : nullptr;
-            const float * res = a.res ? a.res + (size_t) r * a.ldr + col : nullptr;
-            if (full && (a.ldo & 3) == 0 && (!res || (a.ldr & 3) == 0)) {
-                float4 o = v;
-                if (a.bias) {
-                    const float4 b = __ldg(reinterpret_cast<const float4 *>(a.bias + col));
-                    o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
-                }
-                if (gate) {
-                    const float4 g = __ldg(reinterpret_cast<const float4 *>(gate));
-                    o.x *= g.x; o.y *= g.y; o.z *= g.z; o.w *= g.w;
-                }
-                if (res) {
-                    const float4 q = pre[u];
-                    o.x += q.x; o.y += q.y; o.z += q.z; o.w += q.w;
-                }
-                *reinterpret_cast<float4 *>(orow) = o;
-            } else {
+        for (int e = 0; e < 8; ++e) x[e] = __uint_as_float(raw[8 * j + e]);
+        if (a.bias && n + 8 * j < a.N) {
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    if (col + e < a.N) {
-                        float o = x[e];
-                        if (a.bias) o += a.bias[col + e];
-                        if (gate) o *= gate[e];
-                        if (res) o += res[e];
-                        orow[e] = o;
-                    }
-                }
-            }
-        } else if constexpr (EPI == EPI_STORE16 || EPI == EPI_ROPE16) {
-            if (a.bias) {
-#pragma unroll
-                for (int e = 0; e < 4; ++e) if (col + e < a.N) x[e] += a.bias[col + e];
-            }
-            if constexpr (EPI == EPI_ROPE16) {
-                if (col < a.rope_cols) {   // q and k columns; (col, col+1), (col+2, col+3) are rotation pairs
-                    const float4 cs = pre[u];   // (cos,sin) x 2
-                    const float s = col < a.q_cols ? a.q_scale : 1.0f;
-                    const float x0 = x[0], x1 = x[1], y0 = x[2], y1 = x[3];
-                    x[0] = (x0 * cs.x - x1 * cs.y) * s;
-                    x[1] = (x0 * cs.y + x1 * cs.x) * s;
-                    x[2] = (y0 * cs.z - y1 * cs.w) * s;
-                    x[3] = (y0 * cs.w + y1 * cs.z) * s;
-                }
-            }
-            uint16_t * orow = (uint16_t *) a.out + (size_t) r * a.ldo + col;
-            if (full && (a.ldo & 3) == 0) {
-                *reinterpret_cast<uint2 *>(orow) = make_uint2(pack16(x[0], x[1], a.out_dtype), pack16(x[2], x[3], a.out_dtype));
-            } else {
-#pragma unroll
-                for (int e = 0; e < 4; ++e)
-                    if (col + e < a.N) orow[e] = (uint16_t) (pack16(x[e], 0.0f, a.out_dtype) & 0xFFFF);
-            }
-        } else {   // EPI_SWIGLU16: columns (2j, 2j+1) = (gate_j, up_j); N is even
-            uint16_t * orow = (uint16_t *) a.out + (size_t) r * a.ldo + (col >> 1);
-            const float h0 = silu_f(x[0]) * x[1];
-            const float h1 = silu_f(x[2]) * x[3];
-            if (full && (a.ldo & 1) == 0) {
-                *reinterpret_cast<uint32_t *>(orow) = pack16(h0, h1, a.out_dtype);
-            } else {
-                orow[0] = (uint16_t) (pack16(h0, 0.0f, a.out_dtype) & 0xFFFF);
-                if (col + 3 < a.N) orow[1] = (uint16_t) (pack16(h1, 0.0f, a.out_dtype) & 0xFFFF);
+            for (int h = 0; h < 2; ++h) {
+                const float4 b = __ldg(reinterpret_cast<const float4 *>(a.bias + n) + 2 * j + h);
+                x[4 * h] += b.x; x[4 * h + 1] += b.y; x[4 * h + 2] += b.z; x[4 * h + 3] += b.w;
             }
         }
+        if constexpr (ROPE) {
+            if (rotate) {
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const float4 cs = lds128(rrow + (((uint32_t) (2 * j + h) << 4) ^ rsw));   // (cos,sin) of 2 pairs
+                    const float x0 = x[4 * h], x1 = x[4 * h + 1], y0 = x[4 * h + 2], y1 = x[4 * h + 3];
+                    x[4 * h] = (x0 * cs.x - x1 * cs.y) * scale;
+                    x[4 * h + 1] = (x0 * cs.y + x1 * cs.x) * scale;
+                    x[4 * h + 2] = (y0 * cs.z - y1 * cs.w) * scale;
+                    x[4 * h + 3] = (y0 * cs.w + y1 * cs.z) * scale;
+                }
+            }
+        }
+        sts128u(row + (((uint32_t) j << 4) ^ sw), pack16(x[0], x[1], a.out_dtype), pack16(x[2], x[3], a.out_dtype),
+                pack16(x[4], x[5], a.out_dtype), pack16(x[6], x[7], a.out_dtype));
     }
-    __syncwarp();
 }
 
-template <int BN, int EPI, int EW>
+// SwiGLU: 32 accumulator columns (gate_j, up_j interleaved) -> 16 outputs = 16-byte slots 2*half, 2*half+1 of the row
+__device__ __forceinline__ void chunk_swiglu16(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, int lane, int half) {
+    const uint32_t row = buf + lane * 64;
+    const uint32_t sw = (uint32_t) ((lane >> 1) & 3) << 4;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+        uint32_t o[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const float h0 = silu_f(__uint_as_float(raw[16 * j + 4 * e])) * __uint_as_float(raw[16 * j + 4 * e + 1]);
+            const float h1 = silu_f(__uint_as_float(raw[16 * j + 4 * e + 2])) * __uint_as_float(raw[16 * j + 4 * e + 3]);
+            o[e] = pack16(h0, h1, a.out_dtype);
+        }
+        sts128u(row + (((uint32_t) (2 * half + j) << 4) ^ sw), o[0], o[1], o[2], o[3]);
+    }
+}
+
+template <int BN, int EPI, int EW, int NCTA>
 __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __grid_constant__ gemm_args a) {
-    using C = tile_cfg<BN, EW>;
+    using C = tile_cfg<BN, EPI, EW, NCTA>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t bar_base = smem_base + C::STAGES * C::STAGE_BYTES;
-    // barriers: full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2]; then the TMEM base address
+    const uint32_t bar_base = smem_base + C::STAGES * C::STAGE_BYTES + C::EPI_BYTES;   // [stages][epilogue boxes][barriers]
+    // barriers: full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2]; then the TMEM base address.
+    // In a CTA pair both CTAs hold the same block; full[] and tmem_empty[] are only used in the leader (rank 0).
     auto full_bar = [&](int s) { return bar_base + 8u * s; };
     auto empty_bar = [&](int s) { return bar_base + 8u * (C::STAGES + s); };
     auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * C::STAGES + s); };
@@ -266,8 +321,12 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    const int cta_rank = NCTA == 2 ? (int) cluster_ctarank() : 0;
+    const int unit = blockIdx.x / NCTA;            // CTA (pair) index = persistent tile-loop lane
+    const int n_units = gridDim.x / NCTA;
 
-    const int num_m_tiles = (a.M + BLOCK_M - 1) / BLOCK_M;
+    constexpr int TILE_M = BLOCK_M * NCTA;
+    const int num_m_tiles = (a.M + TILE_M - 1) / TILE_M;
     const int num_n_tiles = (a.N + BN - 1) / BN;
     const int num_tiles = num_m_tiles * num_n_tiles;
     const int k_blocks = (a.K + BLOCK_K - 1) / BLOCK_K;
@@ -275,49 +334,69 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < C::STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4 * EW); }
+        for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4 * EW * NCTA); }
+        for (int s = 0; s < 4 * EW * EPI_NBUF; ++s) mbar_init(bar_base + 256u + 8u * s, 1);   // residual boxes
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot),
-                     "r"((uint32_t) C::TMEM_COLS)
-                     : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if constexpr (NCTA == 1) {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot),
+                         "r"((uint32_t) C::TMEM_COLS)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot),
+                         "r"((uint32_t) C::TMEM_COLS)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        }
     }
     tcgen05_fence_before();
-    __syncthreads();
+    if constexpr (NCTA == 2) cluster_sync_all(); else __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot_ptr;
 
     if (warp == 0) {
-        // ===== TMA producer =====
+        // ===== TMA producer (every CTA stages its own A rows and its share of the W tile) =====
         if (lane == 0) {
             uint32_t kit = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-                const int m0 = (t / num_n_tiles) * BLOCK_M;
-                const int n0 = (t % num_n_tiles) * BN;
+            for (int t = unit; t < num_tiles; t += n_units) {
+                const int m0 = (t / num_n_tiles) * TILE_M + cta_rank * BLOCK_M;
+                const int n0 = (t % num_n_tiles) * BN + cta_rank * C::B_ROWS;
                 for (int tap = 0; tap < a.taps; ++tap) {
                     const int arow = m0 + tap - (a.taps >> 1);
                     for (int kb = 0; kb < k_blocks; ++kb, ++kit) {
                         const int s = kit % C::STAGES;
                         mbar_wait(empty_bar(s), ((kit / C::STAGES) & 1) ^ 1);
-                        mbar_expect_tx(full_bar(s), C::STAGE_BYTES);
                         const uint32_t sa = smem_base + s * C::STAGE_BYTES;
-                        tma_load_2d(sa, &a.map_a, full_bar(s), kb * BLOCK_K, arow);
-                        tma_load_2d(sa + C::A_BYTES, &a.map_b, full_bar(s), tap * a.K + kb * BLOCK_K, n0);
+                        if constexpr (NCTA == 1) {
+                            mbar_expect_tx(full_bar(s), C::STAGE_BYTES);
+                            tma_load_2d(sa, &a.map_a, full_bar(s), kb * BLOCK_K, arow);
+#pragma unroll
+                            for (int bx = 0; bx < C::B_ROWS / B_BOX_ROWS; ++bx)
+                                tma_load_2d(sa + C::A_BYTES + bx * (B_BOX_ROWS * BLOCK_K * 2), &a.map_b, full_bar(s),
+                                            tap * a.K + kb * BLOCK_K, n0 + bx * B_BOX_ROWS);
+                        } else {
+                            if (cta_rank == 0) mbar_expect_tx(full_bar(s), 2 * C::STAGE_BYTES);   // both CTAs' bytes
+                            tma_load_2d_pair(sa, &a.map_a, full_bar(s), kb * BLOCK_K, arow);
+#pragma unroll
+                            for (int bx = 0; bx < C::B_ROWS / B_BOX_ROWS; ++bx)
+                                tma_load_2d_pair(sa + C::A_BYTES + bx * (B_BOX_ROWS * BLOCK_K * 2), &a.map_b, full_bar(s),
+                                                 tap * a.K + kb * BLOCK_K, n0 + bx * B_BOX_ROWS);
+                        }
                     }
                 }
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer =====
-        if (lane == 0) {
+        // ===== MMA issuer (leader CTA only) =====
+        if (lane == 0 && cta_rank == 0) {
             // instruction descriptor (cute::UMMA::InstrDescriptor): c=f32 [4,6), a/b format [7,10)/[10,13),
-            // K-major a/b (bits 15,16 = 0), N>>3 [17,23), M>>4 [24,29)
+            // K-major a/b (bits 15,16 = 0), N>>3 [17,23), M>>4 [24,29); M counts the rows of the whole pair
             const uint32_t idesc = (1u << 4) | ((uint32_t) a.dtype << 7) | ((uint32_t) a.dtype << 10) |
-                                   ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (BLOCK_M >> 4) << 24);
+                                   ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (TILE_M >> 4) << 24);
             uint32_t kit = 0, it = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+            for (int t = unit; t < num_tiles; t += n_units, ++it) {
                 const int acc = it & 1;
                 mbar_wait(tempty_bar(acc), ((it >> 1) & 1) ^ 1);
                 tcgen05_fence_after();
@@ -332,61 +411,151 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
 #pragma unroll
                     for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
                         // advance 32 bytes (16 elements) inside the 128B swizzle atom: +2 in the >>4 address field
-                        tcgen05_mma_f16(tmem_d, da + 2 * k, db + 2 * k, idesc, (ki | k) != 0);
+                        tcgen05_mma_f16<NCTA>(tmem_d, da + 2 * k, db + 2 * k, idesc, (ki | k) != 0);
                     }
-                    tcgen05_commit(empty_bar(s));   // frees the smem stage once these MMAs retire
+                    tcgen05_commit<NCTA>(empty_bar(s));   // frees the smem stage (in both CTAs) once these MMAs retire
                 }
-                tcgen05_commit(tfull_bar(acc));     // accumulator complete
+                tcgen05_commit<NCTA>(tfull_bar(acc));     // accumulator complete (signalled in both CTAs)
             }
         }
     } else {
-        // ===== epilogue warps =====
+        // ===== epilogue warps (each CTA drains the accumulator of its own 128 rows) =====
+        using E = epi_cfg<EPI>;
+        constexpr int CPT = BN / E::CW;              // chunks per (tile, lane quadrant)
         const int quad = warp & 3;                   // TMEM lane quadrant this warp may access
         const int ew = warp - 2;                     // epilogue warp index; column group = ew / 4
         const int cgrp = ew >> 2;
-        float * stage = reinterpret_cast<float *>(smem_raw + (bar_base + 256 - smem_u32(smem_raw))) + ew * (32 * EPI_LD);
-        uint32_t it = 0;
-        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
-            const int m0 = (t / num_n_tiles) * BLOCK_M;
+        const uint32_t ebuf = smem_base + C::STAGES * C::STAGE_BYTES + ew * E::WARP_BYTES;
+        const uint32_t rope_st = ebuf + EPI_NBUF * E::BUF_BYTES;
+        auto rbar = [&](int b) { return bar_base + 256u + 8u * (ew * EPI_NBUF + b); };
+        const bool has_res = EPI == EPI_STORE32 && a.res != nullptr;
+
+        auto tile_row0 = [&](int t) { return (t / num_n_tiles) * TILE_M + cta_rank * BLOCK_M + quad * 32; };
+        auto chunk_ok = [&](int t, int c) {
+            return c < CPT && (t % num_n_tiles) * BN + c * E::CW < a.N && tile_row0(t) < a.M;
+        };
+        // residual prefetch cursor: walks this warp's chunks in processing order, across tiles
+        int pf_t = unit, pf_c = cgrp;
+        uint32_t n_ld = 0;
+        auto pf_seek = [&]() { while (pf_t < num_tiles && !chunk_ok(pf_t, pf_c)) { pf_t += n_units; pf_c = cgrp; } };
+        auto pf_issue = [&]() {   // lane 0: TMA-load the residual box of the cursor's chunk, advance the cursor
+            if (pf_t >= num_tiles) return;
+            const int b = n_ld % EPI_NBUF;
+            mbar_expect_tx(rbar(b), E::BUF_BYTES);
+            tma_load_2d(ebuf + b * E::BUF_BYTES, &a.map_out, rbar(b), (pf_t % num_n_tiles) * BN + pf_c * E::CW, tile_row0(pf_t));
+            ++n_ld;
+            pf_c += EW;
+            pf_seek();
+        };
+        if (has_res && lane == 0) {
+            pf_seek();
+            pf_issue();
+            pf_issue();
+        }
+        __syncwarp();
+
+        uint32_t it = 0, nch = 0;                    // tiles / chunks processed by this warp
+        for (int t = unit; t < num_tiles; t += n_units, ++it) {
             const int n0 = (t % num_n_tiles) * BN;
             const int acc = it & 1;
-            const int row0 = m0 + quad * 32;
-            int rmeta[8];
+            const int row0 = tile_row0(t);
+            int rmeta = 0;                           // utterance (gate) or position (rope) of this thread's row
             {
                 const int * mp = EPI == EPI_ROPE16 ? a.row_pos : (EPI == EPI_STORE32 && a.gate ? a.row_utt : nullptr);
-#pragma unroll
-                for (int u = 0; u < 8; ++u) {
-                    const int r = row0 + (lane >> 3) + 4 * u;
-                    rmeta[u] = (mp != nullptr && r < a.M) ? __ldg(mp + r) : 0;
-                }
+                if (mp != nullptr && row0 + lane < a.M) rmeta = max(__ldg(mp + row0 + lane), 0);
             }
             const uint32_t taddr = tmem_base + ((uint32_t) (quad * 32) << 16) + acc * BN;
             mbar_wait(tfull_bar(acc), (it >> 1) & 1);
             tcgen05_fence_after();
 #pragma unroll 1
-            for (int c = cgrp; c < BN / 32; c += EW) {
-                const int n = n0 + c * 32;
-                if (n >= a.N) break;                 // warp-uniform
-                float4 pre[8];
-                epilogue_prefetch<EPI>(a, row0, lane, n, rmeta, pre);
+            for (int c = cgrp; chunk_ok(t, c); c += EW, ++nch) {
+                const int n = n0 + c * E::CW;
+                const int b = nch % EPI_NBUF;
+                const uint32_t buf = ebuf + b * E::BUF_BYTES;
                 uint32_t raw[32];
-                tmem_ld_32x32b_x32(taddr + c * 32, raw);
-                tmem_ld_wait();
-                if (row0 < a.M) epilogue_chunk<EPI>(a, row0, lane, n, raw, stage, rmeta, pre);   // warp-uniform
+                if constexpr (EPI == EPI_ROPE16) {
+                    // this chunk's (cos,sin) rows: coalesced global reads, transposed through the staging tile
+                    const bool rotate = n < a.rope_cols;
+                    if (rotate) {
+                        const int p0 = (n % a.head_dim) >> 1, half = a.head_dim >> 1;
+                        float4 cs[8];
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) {
+                            const int rr = (lane >> 3) + 4 * u;
+                            const int pos = __shfl_sync(0xffffffffu, rmeta, rr);
+                            cs[u] = __ldg(reinterpret_cast<const float4 *>(a.rope + (size_t) pos * half + p0) + (lane & 7));
+                        }
+                        tmem_ld_32x32b_x32(taddr + c * 32, raw);
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) {
+                            const int rr = (lane >> 3) + 4 * u;
+                            sts128(rope_st + rr * 128 + ((uint32_t) ((lane & 7) ^ (rr & 7)) << 4), cs[u]);
+                        }
+                    } else {
+                        tmem_ld_32x32b_x32(taddr + c * 32, raw);
+                    }
+                    if (lane == 0) bulk_wait_read<EPI_NBUF - 1>();
+                    __syncwarp();
+                    tmem_ld_wait();
+                    chunk_store16<true>(a, raw, buf, rope_st, lane, n, rotate, n < a.q_cols ? a.q_scale : 1.0f);
+                } else if constexpr (EPI == EPI_SWIGLU16) {
+                    tmem_ld_32x32b_x32(taddr + c * 64, raw);
+                    if (lane == 0) bulk_wait_read<EPI_NBUF - 1>();
+                    __syncwarp();
+                    tmem_ld_wait();
+                    chunk_swiglu16(a, raw, buf, lane, 0);
+                    tmem_ld_32x32b_x32(taddr + c * 64 + 32, raw);
+                    tmem_ld_wait();
+                    chunk_swiglu16(a, raw, buf, lane, 1);
+                } else if constexpr (EPI == EPI_STORE16) {
+                    tmem_ld_32x32b_x32(taddr + c * 32, raw);
+                    if (lane == 0) bulk_wait_read<EPI_NBUF - 1>();
+                    __syncwarp();
+                    tmem_ld_wait();
+                    chunk_store16<false>(a, raw, buf, 0, lane, n, false, 1.0f);
+                } else {
+                    tmem_ld_32x32b_x32(taddr + c * 32, raw);
+                    if (has_res) mbar_wait(rbar(b), (nch / EPI_NBUF) & 1);       // residual box landed
+                    else { if (lane == 0) bulk_wait_read<EPI_NBUF - 1>(); __syncwarp(); }
+                    tmem_ld_wait();
+                    chunk_store32(a, raw, buf, lane, n, rmeta, has_res);
+                }
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) {
+                    tma_store_2d(&a.map_out, buf, EPI == EPI_SWIGLU16 ? (n >> 1) : n, row0);
+                    bulk_commit();
+                    if (has_res) {
+                        // the box of chunk nch-1 is the next prefetch target: its store must have read smem
+                        bulk_wait_read<1>();
+                        pf_issue();
+                    }
+                }
             }
             tcgen05_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(tempty_bar(acc));
+            if (lane == 0) {
+                if constexpr (NCTA == 1) mbar_arrive(tempty_bar(acc));
+                else mbar_arrive_leader(tempty_bar(acc));
+            }
         }
+        if (lane == 0) bulk_wait_all();              // smem must outlive the last stores' reads
+        __syncwarp();
     }
 
     tcgen05_fence_before();
-    __syncthreads();
+    if constexpr (NCTA == 2) cluster_sync_all(); else __syncthreads();
     if (warp == 1) {
         tcgen05_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
-                     "r"((uint32_t) C::TMEM_COLS)
-                     : "memory");
+        if constexpr (NCTA == 1) {
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                         "r"((uint32_t) C::TMEM_COLS)
+                         : "memory");
+        } else {
+            asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                         "r"((uint32_t) C::TMEM_COLS)
+                         : "memory");
+        }
     }
 }
 
@@ -409,29 +578,39 @@ encode_tiled_fn get_encode_fn() {
     return fn;
 }
 
-template <int BN, int EPI, int EW> void launch_t(const gemm_args & a, int num_sms, cudaStream_t st) {
-    using C = tile_cfg<BN, EW>;
+template <int BN, int EPI, int EW, int NCTA> void launch_t(const gemm_args & a, int num_sms, cudaStream_t st) {
+    using C = tile_cfg<BN, EPI, EW, NCTA>;
     static bool configured[64] = {false};   // per-device function attribute
     int dev = 0;
     MIO_CUDA(cudaGetDevice(&dev));
     if (!configured[dev & 63]) {
-        MIO_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, EPI, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        MIO_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, EPI, EW, NCTA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       C::SMEM_BYTES));
         configured[dev & 63] = true;
     }
-    const int tiles = ((a.M + BLOCK_M - 1) / BLOCK_M) * ((a.N + BN - 1) / BN);
-    const int grid = tiles < num_sms ? tiles : num_sms;
-    gemm_tcgen05_kernel<BN, EPI, EW><<<grid, C::THREADS, C::SMEM_BYTES, st>>>(a);
-    MIO_CUDA(cudaGetLastError());
+    const int tiles = ((a.M + BLOCK_M * NCTA - 1) / (BLOCK_M * NCTA)) * ((a.N + BN - 1) / BN);
+    const int units = num_sms / NCTA;
+    cudaLaunchConfig_t cfg;
+    std::memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned) (NCTA * (tiles < units ? tiles : units)));
+    cfg.blockDim = dim3(C::THREADS);
+    cfg.dynamicSmemBytes = C::SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = NCTA; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    MIO_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN, EPI, EW, NCTA>, a));
     count_launch();
 }
 
-template <int BN, int EW> void launch_bn(const gemm_args & a, int num_sms, cudaStream_t st) {
+template <int BN, int EW, int NCTA> void launch_bn(const gemm_args & a, int num_sms, cudaStream_t st) {
     switch (a.epilogue) {
-        case EPI_STORE32: launch_t<BN, EPI_STORE32, EW>(a, num_sms, st); break;
-        case EPI_STORE16: launch_t<BN, EPI_STORE16, EW>(a, num_sms, st); break;
-        case EPI_SWIGLU16: launch_t<BN, EPI_SWIGLU16, EW>(a, num_sms, st); break;
-        case EPI_ROPE16: launch_t<BN, EPI_ROPE16, EW>(a, num_sms, st); break;
+        case EPI_STORE32: launch_t<BN, EPI_STORE32, EW, NCTA>(a, num_sms, st); break;
+        case EPI_STORE16: launch_t<BN, EPI_STORE16, EW, NCTA>(a, num_sms, st); break;
+        case EPI_SWIGLU16: launch_t<BN, EPI_SWIGLU16, EW, NCTA>(a, num_sms, st); break;
+        case EPI_ROPE16: launch_t<BN, EPI_ROPE16, EW, NCTA>(a, num_sms, st); break;
         default: throw cuda_error("gemm: bad epilogue");
     }
 }
@@ -439,13 +618,14 @@ template <int BN, int EW> void launch_bn(const gemm_args & a, int num_sms, cudaS
 } // namespace
 
 int gemm_block_n(int N) { return N >= 256 ? 256 : 128; }
+int gemm_w_box_rows() { return B_BOX_ROWS; }
 
 CUtensorMap make_tmap_16(const void * ptr, uint64_t rows, uint64_t cols, uint32_t box_rows) {
     if ((cols % 8) != 0) throw cuda_error("tensor map: row pitch must be a multiple of 16 bytes");
     CUtensorMap m;
     const cuuint64_t dims[2] = {cols, rows};
     const cuuint64_t strides[1] = {cols * 2};
-    const cuuint32_t box[2] = {(cuuint32_t) BLOCK_K, box_rows};
+    const cuuint32_t box[2] = {(cuuint32_t) BLOCK_K, box_rows};   // W maps: box_rows = gemm_w_box_rows()
     const cuuint32_t estr[2] = {1, 1};
     const CUresult r = get_encode_fn()(&m, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, const_cast<void *>(ptr), dims, strides,
                                        box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -454,23 +634,40 @@ CUtensorMap make_tmap_16(const void * ptr, uint64_t rows, uint64_t cols, uint32_
     return m;
 }
 
+CUtensorMap make_tmap_out(const void * ptr, uint64_t rows, uint64_t cols, uint64_t ld_elems, int elem_bytes) {
+    if (elem_bytes != 2 && elem_bytes != 4) throw cuda_error("output tensor map: element size must be 2 or 4");
+    if (((uintptr_t) ptr & 15) != 0 || (ld_elems * elem_bytes) % 16 != 0)
+        throw cuda_error("output tensor map: base and row pitch must be multiples of 16 bytes");
+    CUtensorMap m;
+    const cuuint64_t dims[2] = {cols, rows};
+    const cuuint64_t strides[1] = {ld_elems * (uint64_t) elem_bytes};
+    const cuuint32_t box[2] = {32, 32};    // one epilogue chunk: 32 rows x 32 elements (128 B fp32 / 64 B 16-bit rows)
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = get_encode_fn()(&m, elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_UINT16, 2,
+                                       const_cast<void *>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                       elem_bytes == 4 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                                       CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) throw cuda_error("cuTensorMapEncodeTiled (output) failed: " + std::to_string((int) r));
+    return m;
+}
+
 void gemm_launch(const gemm_args & a, int num_sms, cudaStream_t st) {
     if (a.M <= 0 || a.N <= 0 || a.K <= 0) return;
     if (a.epilogue == EPI_ROPE16 && (a.head_dim % 32) != 0) throw cuda_error("gemm: rope epilogue needs head_dim % 32 == 0");
-    static int ew = -1;
-    if (ew < 0) {   // epilogue warps per TMEM quadrant: memory-level parallelism of the residual read-modify-write
+    if (a.res != nullptr && a.res != a.out) throw cuda_error("gemm: the residual must be the (in-place) output");
+    static int ew = -1, ncta = -1;
+    if (ew < 0) {   // epilogue warps per TMEM lane quadrant
         const char * e = std::getenv("MIO_TTS_B200_GEMM_EW");
-        ew = e ? std::atoi(e) : 4;
-        if (ew != 1 && ew != 2 && ew != 4) ew = 4;
+        ew = e ? std::atoi(e) : 2;
+        if (ew != 1 && ew != 2) ew = 2;
+        const char * c = std::getenv("MIO_TTS_B200_GEMM_CTA");   // 1 = single-CTA tiles everywhere (A/B testing)
+        ncta = (c && std::atoi(c) == 1) ? 1 : 2;
     }
     if (gemm_block_n(a.N) == 256) {
-        if (ew == 1) launch_bn<256, 1>(a, num_sms, st);
-        else if (ew == 2) launch_bn<256, 2>(a, num_sms, st);
-        else launch_bn<256, 4>(a, num_sms, st);
+        if (ncta == 2) { if (ew == 1) launch_bn<256, 1, 2>(a, num_sms, st); else launch_bn<256, 2, 2>(a, num_sms, st); }
+        else { if (ew == 1) launch_bn<256, 1, 1>(a, num_sms, st); else launch_bn<256, 2, 1>(a, num_sms, st); }
     } else {
-        if (ew == 1) launch_bn<128, 1>(a, num_sms, st);
-        else if (ew == 2) launch_bn<128, 2>(a, num_sms, st);
-        else launch_bn<128, 4>(a, num_sms, st);
+        if (ew == 1) launch_bn<128, 1, 1>(a, num_sms, st); else launch_bn<128, 2, 1>(a, num_sms, st);
     }
 }
 

@@ -84,7 +84,7 @@ struct loader {
         L.w16 = m.dalloc(n_pad * (size_t) taps * K * 2);
         MIO_CUDA(cudaMemset(L.w16, 0, n_pad * (size_t) taps * K * 2));
         MIO_CUDA(cudaMemcpy(L.w16, h.data(), h.size() * 2, cudaMemcpyHostToDevice));
-        L.map_b = make_tmap_16(L.w16, (uint64_t) N, (uint64_t) taps * K, (uint32_t) bn);
+        L.map_b = make_tmap_16(L.w16, (uint64_t) N, (uint64_t) taps * K, (uint32_t) gemm_w_box_rows());
         if (bias) {
             std::vector<float> bp(((size_t) N + 3) / 4 * 4, 0.0f);
             std::copy(bias->begin(), bias->end(), bp.begin());

@@ -47,21 +47,43 @@ __global__ void gather_kernel(const float * __restrict__ table, const int * __re
 
 // ---- AdaLN conditioning: p = W * silu(emb) + b for every conditioned norm at once
 //      (src/miocodec-decoder.cpp:1164-1181 cond = silu(embedding); :1204-1210, :1271-1277, :1390-1400) ----
-__global__ void cond_kernel(const float * __restrict__ w, const float * __restrict__ b,
-                            const float * __restrict__ emb, float * __restrict__ out, int n_out, int adim,
-                            int n_utt) {
-    const int j = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (j >= n_out) return;
-    const int lane = threadIdx.x & 31;
-    const float * wr = w + (size_t) j * adim;
-    const float bj = b[j];
-    // 16 utterances per block so a weight row is fetched from L2 once per 16 dot products
-    for (int utt = blockIdx.y * 16; utt < min(n_utt, (int) blockIdx.y * 16 + 16); ++utt) {
-        const float * e = emb + (size_t) utt * adim;
-        float acc = 0.0f;
-        for (int i = lane; i < adim; i += 32) acc += __ldg(wr + i) * silu_exact(e[i]);
-        acc = warp_sum(acc);
-        if (lane == 0) out[(size_t) utt * n_out + j] = acc + bj;
+// Block = 64 utterances x 16 output rows: silu(emb) of the 64 utterances and the 16 weight rows are staged in shared
+// memory once, each thread owns one utterance and 4 consecutive rows (weight reads are warp broadcasts, embedding
+// reads are conflict-free through the +1 row padding).
+constexpr int COND_UTT = 64, COND_ROWS = 16;
+__global__ void __launch_bounds__(256) cond_kernel(const float * __restrict__ w, const float * __restrict__ b,
+                                                   const float * __restrict__ emb, float * __restrict__ out, int n_out,
+                                                   int adim, int n_utt) {
+    extern __shared__ float cond_smem[];
+    float * es = cond_smem;                                  // [COND_UTT][adim + 1]
+    float * ws = cond_smem + COND_UTT * (adim + 1);          // [COND_ROWS][adim]
+    const int utt0 = blockIdx.y * COND_UTT, j0 = blockIdx.x * COND_ROWS;
+    for (int i = threadIdx.x; i < COND_UTT * adim; i += blockDim.x) {
+        const int u = i / adim, k = i - u * adim;
+        es[u * (adim + 1) + k] = utt0 + u < n_utt ? silu_exact(emb[(size_t) (utt0 + u) * adim + k]) : 0.0f;
+    }
+    for (int i = threadIdx.x; i < COND_ROWS * adim; i += blockDim.x) {
+        const int r = i / adim;
+        ws[i] = j0 + r < n_out ? __ldg(w + (size_t) j0 * adim + i) : 0.0f;
+    }
+    __syncthreads();
+    const int u = threadIdx.x & (COND_UTT - 1), jg = threadIdx.x / COND_UTT;
+    const float * e = es + u * (adim + 1);
+    const float * wr = ws + jg * 4 * adim;
+    float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+    for (int k = 0; k < adim; ++k) {
+        const float ev = e[k];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) acc[r] = fmaf(wr[r * adim + k], ev, acc[r]);
+    }
+    if (utt0 + u >= n_utt) return;
+    const int j = j0 + jg * 4;
+    float * o = out + (size_t) (utt0 + u) * n_out + j;
+    if (j + 4 <= n_out && (n_out & 3) == 0) {
+        *reinterpret_cast<float4 *>(o) = make_float4(acc[0] + b[j], acc[1] + b[j + 1], acc[2] + b[j + 2], acc[3] + b[j + 3]);
+    } else {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) if (j + r < n_out) o[r] = acc[r] + b[j + r];
     }
 }
 
@@ -388,8 +410,17 @@ void launch_gather(const float * table, const int * codes, float * out, int n_ro
 void launch_cond(const float * w, const float * b, const float * emb, float * out, int n_out, int adim, int n_utt,
                  cudaStream_t st) {
     if (n_out <= 0 || n_utt <= 0) return;
-    dim3 grid(blocks_for((size_t) n_out, 8), (unsigned) ((n_utt + 15) / 16));
-    cond_kernel<<<grid, 256, 0, st>>>(w, b, emb, out, n_out, adim, n_utt);
+    dim3 grid(blocks_for((size_t) n_out, COND_ROWS), (unsigned) ((n_utt + COND_UTT - 1) / COND_UTT));
+    const size_t smem = ((size_t) COND_UTT * (adim + 1) + (size_t) COND_ROWS * adim) * sizeof(float);
+    if (smem > 200 * 1024) throw cuda_error("cond: adanorm dimension too large");
+    static bool configured[64] = {false};
+    int dev = 0;
+    MIO_CUDA(cudaGetDevice(&dev));
+    if (smem > 48 * 1024 && !configured[dev & 63]) {
+        MIO_CUDA(cudaFuncSetAttribute(cond_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        configured[dev & 63] = true;
+    }
+    cond_kernel<<<grid, 256, smem, st>>>(w, b, emb, out, n_out, adim, n_utt);
     MIO_CUDA(cudaGetLastError());
     count_launch();
 }
