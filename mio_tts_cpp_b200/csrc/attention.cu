@@ -48,6 +48,7 @@ template <bool BF16>
 __global__ void __launch_bounds__(128) attention_band_kernel(const uint16_t * __restrict__ qkv,
                                                              uint16_t * __restrict__ out, int dim, int half_window,
                                                              const row_tile * __restrict__ tiles) {
+    MIO_PDL_PROLOGUE();
     __shared__ __align__(16) uint16_t Qs[TQ * LDS];
     __shared__ __align__(16) uint16_t Ks[TK * LDS];
     __shared__ __align__(16) uint16_t Vs[TK * LDS];
@@ -201,6 +202,7 @@ template <bool BF16> __device__ __forceinline__ uint16_t st16(float v) {
 template <bool BF16>
 __global__ void attention_generic_kernel(const uint16_t * __restrict__ qkv, uint16_t * __restrict__ out, int dim,
                                          int head_dim, int half_window, const row_tile * __restrict__ tiles) {
+    MIO_PDL_PROLOGUE();
     extern __shared__ float sc[];   // [warps][2*half_window+1]
     const row_tile t = tiles[blockIdx.x];
     const int head = blockIdx.y;
@@ -249,13 +251,13 @@ void launch_attention(const void * qkv16, void * out16, int dtype, int dim, int 
     const uint16_t * q = (const uint16_t *) qkv16;
     uint16_t * o = (uint16_t *) out16;
     if (!force_generic && head_dim == HD && half <= 32 && (dim % 8) == 0) {
-        if (dtype == OP_BF16) attention_band_kernel<true><<<grid, 128, 0, st>>>(q, o, dim, half, tiles);
-        else attention_band_kernel<false><<<grid, 128, 0, st>>>(q, o, dim, half, tiles);
+        if (dtype == OP_BF16) launch_pdl(attention_band_kernel<true>, dim3(grid), dim3(128), 0, st, q, o, dim, half, tiles);
+        else launch_pdl(attention_band_kernel<false>, dim3(grid), dim3(128), 0, st, q, o, dim, half, tiles);
     } else {
         const size_t smem = 4 * (size_t) (2 * half + 1) * sizeof(float);
         if (smem > 48 * 1024) throw cuda_error("attention: window too large for the generic kernel");
-        if (dtype == OP_BF16) attention_generic_kernel<true><<<grid, 128, smem, st>>>(q, o, dim, head_dim, half, tiles);
-        else attention_generic_kernel<false><<<grid, 128, smem, st>>>(q, o, dim, head_dim, half, tiles);
+        if (dtype == OP_BF16) launch_pdl(attention_generic_kernel<true>, dim3(grid), dim3(128), smem, st, q, o, dim, head_dim, half, tiles);
+        else launch_pdl(attention_generic_kernel<false>, dim3(grid), dim3(128), smem, st, q, o, dim, head_dim, half, tiles);
     }
     MIO_CUDA(cudaGetLastError());
     count_launch();

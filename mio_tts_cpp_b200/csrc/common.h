@@ -25,6 +25,30 @@ inline void cuda_check(cudaError_t e, const char * what, const char * file, int 
 extern std::atomic<unsigned long long> g_launch_count;
 inline void count_launch(int n = 1) { g_launch_count.fetch_add((unsigned long long) n, std::memory_order_relaxed); }
 
+// ---------------------------------------------------------------------------------------------
+// Programmatic dependent launch.  A decode step is ~140 short kernels back to back on one stream; each is launched
+// with programmaticStreamSerialization so its CTAs are scheduled (and run their prologue: barrier init, TMEM
+// allocation, index math) while the previous kernel drains.  Every kernel starts with MIO_PDL_PROLOGUE():
+// launch_dependents lets the NEXT kernel be scheduled early, wait blocks until the PREVIOUS grid has completed and
+// its writes are visible (completion is transitive because every kernel waits).  MIO_TTS_B200_PDL=0 disables it.
+// ---------------------------------------------------------------------------------------------
+bool pdl_enabled();
+#ifdef __CUDACC__
+#define MIO_PDL_TRIGGER() asm volatile("griddepcontrol.launch_dependents;" ::: "memory")
+#define MIO_PDL_WAIT() asm volatile("griddepcontrol.wait;" ::: "memory")
+#define MIO_PDL_PROLOGUE() do { MIO_PDL_TRIGGER(); MIO_PDL_WAIT(); } while (0)
+template <typename... KArgs, typename... Args>
+inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args &&... args) {
+    cudaLaunchConfig_t cfg;
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    MIO_CUDA(cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...));
+}
+#endif
+
 // 16-bit operand formats of the tensor-core GEMMs (tcgen05 kind::f16 a/b_format field)
 enum op16 : int { OP_F16 = 0, OP_BF16 = 1 };
 
@@ -49,7 +73,7 @@ enum gemm_epilogue : int {
     EPI_STORE32 = 0,   // out32[r,n] = (acc + bias[n]) * gate[utt(r),n] + res[r,n]   (each term optional)
     EPI_STORE16 = 1,   // out16[r,n] = acc + bias[n]
     EPI_SWIGLU16 = 2,  // out16[r,n/2] = silu(acc[r,2j]) * acc[r,2j+1]   (weights interleaved gate/up)
-    EPI_ROPE16 = 3,    // out16[r,n] = rope(acc) for n < rope_cols (q,k), q scaled; plain for v
+    EPI_ROPE16 = 3,    // out16[r,n] = rope(acc) for n < rope_cols (q,k); plain for v
 };
 
 struct gemm_args {
@@ -67,7 +91,7 @@ struct gemm_args {
     const int * row_utt;                 // row -> utterance (needed with gate)
     const int * row_pos;                 // row -> position in utterance (needed with rope)
     const float2 * rope;                 // [pos, head_dim/2] (cos, sin)
-    int rope_cols, head_dim, q_cols; float q_scale;
+    int rope_cols, head_dim;             // columns [0, rope_cols) = q,k: rotated in (even, odd) pairs per head
 };
 
 void gemm_launch(const gemm_args & a, int num_sms, cudaStream_t st);

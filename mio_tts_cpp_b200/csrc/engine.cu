@@ -394,8 +394,7 @@ void engine::gemm(const dbuf & a, const dev_linear & w, int M, int epilogue, voi
     g.row_pos = lay ? lay->d_row_pos : nullptr;
     if (epilogue == EPI_ROPE16) {
         const int dim = w.N / 3;
-        g.rope = rope; g.rope_cols = 2 * dim; g.q_cols = dim; g.head_dim = dim / heads;
-        g.q_scale = 1.0f / sqrtf((float) g.head_dim);
+        g.rope = rope; g.rope_cols = 2 * dim; g.head_dim = dim / heads;   // (the 1/sqrt(head_dim) q scale lives in Wq)
     }
     size_t evi = 0;
     if (prof_gemm_) {

@@ -220,27 +220,30 @@ __device__ __forceinline__ float silu_f(float x) { return __fdividef(x, 1.0f + _
 // Output boxes in shared memory use the TMA swizzle of their tensor map so that a quarter-warp's 16-byte accesses
 // hit 32 distinct banks: SWIZZLE_128B for 128-byte rows (fp32), SWIZZLE_64B for 64-byte rows (16-bit).
 
-// fp32 box: out = (acc + bias) * gate + residual, residual read from / result written to the same box slot
+// fp32 box: out = (acc + bias) * gate + residual, residual read from / result written to the same box slot.
+// BIAS/GATE/RES are compile-time so an absent term costs no issue slots; GUARD handles the last, partial N tile.
+template <bool BIAS, bool GATE, bool RES, bool GUARD>
 __device__ __forceinline__ void chunk_store32(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, int lane, int n,
-                                              int utt, bool has_res) {
+                                              const float * gate_row) {
     const uint32_t row = buf + lane * 128;
     const uint32_t sw = (uint32_t) (lane & 7) << 4;
-    const float * gate = a.gate ? a.gate + (size_t) utt * a.gate_ld + n : nullptr;
+    const float4 * bias4 = reinterpret_cast<const float4 *>(a.bias + n);
+    const float4 * gate4 = reinterpret_cast<const float4 *>(gate_row + n);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         const uint32_t addr = row + (((uint32_t) j << 4) ^ sw);
         float4 o = make_float4(__uint_as_float(raw[4 * j]), __uint_as_float(raw[4 * j + 1]), __uint_as_float(raw[4 * j + 2]),
                                __uint_as_float(raw[4 * j + 3]));
-        const bool in = n + 4 * j < a.N;      // columns past N are clipped by the TMA store; do not read past the vectors
-        if (a.bias && in) {
-            const float4 b = __ldg(reinterpret_cast<const float4 *>(a.bias + n) + j);
+        const bool in = !GUARD || n + 4 * j < a.N;   // columns past N are clipped by the TMA store; do not read past the vectors
+        if (BIAS && in) {
+            const float4 b = __ldg(bias4 + j);
             o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
         }
-        if (gate && in) {
-            const float4 g = __ldg(reinterpret_cast<const float4 *>(gate) + j);
+        if (GATE && in) {
+            const float4 g = __ldg(gate4 + j);
             o.x *= g.x; o.y *= g.y; o.z *= g.z; o.w *= g.w;
         }
-        if (has_res) {
+        if (RES) {
             const float4 q = lds128(addr);
             o.x += q.x; o.y += q.y; o.z += q.z; o.w += q.w;
         }
@@ -248,10 +251,40 @@ __device__ __forceinline__ void chunk_store32(const gemm_args & a, const uint32_
     }
 }
 
-// 16-bit box of 32 columns (+ bias); RoPE on (even, odd) column pairs with this row's (cos, sin) from the staging tile
-template <bool ROPE>
+__device__ __forceinline__ void chunk_store32_any(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, int lane, int n,
+                                                  const float * gate_row, bool has_res) {
+    // warp-uniform dispatch to the term combinations the decoder uses
+    if (n + 32 <= a.N) {
+        if (a.gate) { if (a.bias) chunk_store32<true, true, true, false>(a, raw, buf, lane, n, gate_row);
+                      else chunk_store32<false, true, true, false>(a, raw, buf, lane, n, gate_row); }
+        else if (has_res) { if (a.bias) chunk_store32<true, false, true, false>(a, raw, buf, lane, n, gate_row);
+                            else chunk_store32<false, false, true, false>(a, raw, buf, lane, n, gate_row); }
+        else { if (a.bias) chunk_store32<true, false, false, false>(a, raw, buf, lane, n, gate_row);
+               else chunk_store32<false, false, false, false>(a, raw, buf, lane, n, gate_row); }
+    } else {
+        if (a.gate) { if (a.bias) chunk_store32<true, true, true, true>(a, raw, buf, lane, n, gate_row);
+                      else chunk_store32<false, true, true, true>(a, raw, buf, lane, n, gate_row); }
+        else if (has_res) { if (a.bias) chunk_store32<true, false, true, true>(a, raw, buf, lane, n, gate_row);
+                            else chunk_store32<false, false, true, true>(a, raw, buf, lane, n, gate_row); }
+        else { if (a.bias) chunk_store32<true, false, false, true>(a, raw, buf, lane, n, gate_row);
+               else chunk_store32<false, false, false, true>(a, raw, buf, lane, n, gate_row); }
+    }
+}
+
+template <bool BF16> __device__ __forceinline__ uint32_t pack16t(float a, float b) {
+    if constexpr (BF16) {
+        __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+        return *reinterpret_cast<uint32_t *>(&v);
+    } else {
+        __half2 v = __floats2half2_rn(a, b);
+        return *reinterpret_cast<uint32_t *>(&v);
+    }
+}
+
+// 16-bit box of 32 columns (+ bias); ROPE rotates (even, odd) column pairs by this row's (cos, sin) from the staging tile
+template <bool ROPE, bool BIAS, bool BF16>
 __device__ __forceinline__ void chunk_store16(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, uint32_t rope_st,
-                                              int lane, int n, bool rotate, float scale) {
+                                              int lane, int n) {
     const uint32_t row = buf + lane * 64;
     const uint32_t sw = (uint32_t) ((lane >> 1) & 3) << 4;
     const uint32_t rrow = rope_st + lane * 128;
@@ -261,7 +294,7 @@ __device__ __forceinline__ void chunk_store16(const gemm_args & a, const uint32_
         float x[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) x[e] = __uint_as_float(raw[8 * j + e]);
-        if (a.bias && n + 8 * j < a.N) {
+        if (BIAS && n + 8 * j < a.N) {
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 const float4 b = __ldg(reinterpret_cast<const float4 *>(a.bias + n) + 2 * j + h);
@@ -269,25 +302,34 @@ __device__ __forceinline__ void chunk_store16(const gemm_args & a, const uint32_
             }
         }
         if constexpr (ROPE) {
-            if (rotate) {
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const float4 cs = lds128(rrow + (((uint32_t) (2 * j + h) << 4) ^ rsw));   // (cos,sin) of 2 pairs
-                    const float x0 = x[4 * h], x1 = x[4 * h + 1], y0 = x[4 * h + 2], y1 = x[4 * h + 3];
-                    x[4 * h] = (x0 * cs.x - x1 * cs.y) * scale;
-                    x[4 * h + 1] = (x0 * cs.y + x1 * cs.x) * scale;
-                    x[4 * h + 2] = (y0 * cs.z - y1 * cs.w) * scale;
-                    x[4 * h + 3] = (y0 * cs.w + y1 * cs.z) * scale;
-                }
+            for (int h = 0; h < 2; ++h) {
+                const float4 cs = lds128(rrow + (((uint32_t) (2 * j + h) << 4) ^ rsw));   // (cos,sin) of 2 pairs
+                const float x0 = x[4 * h], x1 = x[4 * h + 1], y0 = x[4 * h + 2], y1 = x[4 * h + 3];
+                x[4 * h] = x0 * cs.x - x1 * cs.y;
+                x[4 * h + 1] = x0 * cs.y + x1 * cs.x;
+                x[4 * h + 2] = y0 * cs.z - y1 * cs.w;
+                x[4 * h + 3] = y0 * cs.w + y1 * cs.z;
             }
         }
-        sts128u(row + (((uint32_t) j << 4) ^ sw), pack16(x[0], x[1], a.out_dtype), pack16(x[2], x[3], a.out_dtype),
-                pack16(x[4], x[5], a.out_dtype), pack16(x[6], x[7], a.out_dtype));
+        sts128u(row + (((uint32_t) j << 4) ^ sw), pack16t<BF16>(x[0], x[1]), pack16t<BF16>(x[2], x[3]),
+                pack16t<BF16>(x[4], x[5]), pack16t<BF16>(x[6], x[7]));
     }
 }
 
+template <bool ROPE>
+__device__ __forceinline__ void chunk_store16_any(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, uint32_t rope_st,
+                                                  int lane, int n) {
+    const bool bf16 = a.out_dtype == OP_BF16;   // warp-uniform
+    if (a.bias) { if (bf16) chunk_store16<ROPE, true, true>(a, raw, buf, rope_st, lane, n);
+                  else chunk_store16<ROPE, true, false>(a, raw, buf, rope_st, lane, n); }
+    else { if (bf16) chunk_store16<ROPE, false, true>(a, raw, buf, rope_st, lane, n);
+           else chunk_store16<ROPE, false, false>(a, raw, buf, rope_st, lane, n); }
+}
+
 // SwiGLU: 32 accumulator columns (gate_j, up_j interleaved) -> 16 outputs = 16-byte slots 2*half, 2*half+1 of the row
-__device__ __forceinline__ void chunk_swiglu16(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, int lane, int half) {
+template <bool BF16>
+__device__ __forceinline__ void chunk_swiglu16(const uint32_t (&raw)[32], uint32_t buf, int lane, int half) {
     const uint32_t row = buf + lane * 64;
     const uint32_t sw = (uint32_t) ((lane >> 1) & 3) << 4;
 #pragma unroll
@@ -297,7 +339,7 @@ __device__ __forceinline__ void chunk_swiglu16(const gemm_args & a, const uint32
         for (int e = 0; e < 4; ++e) {
             const float h0 = silu_f(__uint_as_float(raw[16 * j + 4 * e])) * __uint_as_float(raw[16 * j + 4 * e + 1]);
             const float h1 = silu_f(__uint_as_float(raw[16 * j + 4 * e + 2])) * __uint_as_float(raw[16 * j + 4 * e + 3]);
-            o[e] = pack16(h0, h1, a.out_dtype);
+            o[e] = pack16t<BF16>(h0, h1);
         }
         sts128u(row + (((uint32_t) (2 * half + j) << 4) ^ sw), o[0], o[1], o[2], o[3]);
     }
@@ -306,6 +348,7 @@ __device__ __forceinline__ void chunk_swiglu16(const gemm_args & a, const uint32
 template <int BN, int EPI, int EW, int NCTA>
 __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __grid_constant__ gemm_args a) {
     using C = tile_cfg<BN, EPI, EW, NCTA>;
+    MIO_PDL_TRIGGER();   // the next kernel's CTAs may be scheduled as ours retire; it waits for our completion itself
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t bar_base = smem_base + C::STAGES * C::STAGE_BYTES + C::EPI_BYTES;   // [stages][epilogue boxes][barriers]
@@ -355,6 +398,7 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
     if constexpr (NCTA == 2) cluster_sync_all(); else __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot_ptr;
+    MIO_PDL_WAIT();      // barriers and TMEM are set up; from here on we touch memory the previous kernel wrote
 
     if (warp == 0) {
         // ===== TMA producer (every CTA stages its own A rows and its share of the W tile) =====
@@ -459,10 +503,22 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
             const int n0 = (t % num_n_tiles) * BN;
             const int acc = it & 1;
             const int row0 = tile_row0(t);
-            int rmeta = 0;                           // utterance (gate) or position (rope) of this thread's row
-            {
-                const int * mp = EPI == EPI_ROPE16 ? a.row_pos : (EPI == EPI_STORE32 && a.gate ? a.row_utt : nullptr);
-                if (mp != nullptr && row0 + lane < a.M) rmeta = max(__ldg(mp + row0 + lane), 0);
+            // per-row operands of this tile: the AdaLN gate vector of the row's utterance (STORE32), or the rope-table
+            // rows this lane fetches for the transposed (cos,sin) staging (ROPE16: row (lane>>3)+4u, 16-byte slot lane&7)
+            const float * gate_row = nullptr;
+            const float4 * rope_row[EPI == EPI_ROPE16 ? 8 : 1];
+            if constexpr (EPI == EPI_STORE32) {
+                if (a.gate) {
+                    const int utt = row0 + lane < a.M ? max(__ldg(a.row_utt + row0 + lane), 0) : 0;
+                    gate_row = a.gate + (size_t) utt * a.gate_ld;
+                }
+            } else if constexpr (EPI == EPI_ROPE16) {
+                const int pos = row0 + lane < a.M ? max(__ldg(a.row_pos + row0 + lane), 0) : 0;
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int p = __shfl_sync(0xffffffffu, pos, (lane >> 3) + 4 * u);
+                    rope_row[u] = reinterpret_cast<const float4 *>(a.rope + (size_t) p * (a.head_dim >> 1)) + (lane & 7);
+                }
             }
             const uint32_t taddr = tmem_base + ((uint32_t) (quad * 32) << 16) + acc * BN;
             mbar_wait(tfull_bar(acc), (it >> 1) & 1);
@@ -477,14 +533,10 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
                     // this chunk's (cos,sin) rows: coalesced global reads, transposed through the staging tile
                     const bool rotate = n < a.rope_cols;
                     if (rotate) {
-                        const int p0 = (n % a.head_dim) >> 1, half = a.head_dim >> 1;
+                        const int p0 = (n % a.head_dim) >> 2;    // first pair of the chunk, in float4 (2-pair) units
                         float4 cs[8];
 #pragma unroll
-                        for (int u = 0; u < 8; ++u) {
-                            const int rr = (lane >> 3) + 4 * u;
-                            const int pos = __shfl_sync(0xffffffffu, rmeta, rr);
-                            cs[u] = __ldg(reinterpret_cast<const float4 *>(a.rope + (size_t) pos * half + p0) + (lane & 7));
-                        }
+                        for (int u = 0; u < 8; ++u) cs[u] = __ldg(rope_row[u] + p0);
                         tmem_ld_32x32b_x32(taddr + c * 32, raw);
 #pragma unroll
                         for (int u = 0; u < 8; ++u) {
@@ -497,28 +549,36 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
                     if (lane == 0) bulk_wait_read<EPI_NBUF - 1>();
                     __syncwarp();
                     tmem_ld_wait();
-                    chunk_store16<true>(a, raw, buf, rope_st, lane, n, rotate, n < a.q_cols ? a.q_scale : 1.0f);
+                    if (rotate) chunk_store16_any<true>(a, raw, buf, rope_st, lane, n);
+                    else chunk_store16_any<false>(a, raw, buf, rope_st, lane, n);
                 } else if constexpr (EPI == EPI_SWIGLU16) {
                     tmem_ld_32x32b_x32(taddr + c * 64, raw);
                     if (lane == 0) bulk_wait_read<EPI_NBUF - 1>();
                     __syncwarp();
                     tmem_ld_wait();
-                    chunk_swiglu16(a, raw, buf, lane, 0);
-                    tmem_ld_32x32b_x32(taddr + c * 64 + 32, raw);
-                    tmem_ld_wait();
-                    chunk_swiglu16(a, raw, buf, lane, 1);
+                    if (a.out_dtype == OP_BF16) {
+                        chunk_swiglu16<true>(raw, buf, lane, 0);
+                        tmem_ld_32x32b_x32(taddr + c * 64 + 32, raw);
+                        tmem_ld_wait();
+                        chunk_swiglu16<true>(raw, buf, lane, 1);
+                    } else {
+                        chunk_swiglu16<false>(raw, buf, lane, 0);
+                        tmem_ld_32x32b_x32(taddr + c * 64 + 32, raw);
+                        tmem_ld_wait();
+                        chunk_swiglu16<false>(raw, buf, lane, 1);
+                    }
                 } else if constexpr (EPI == EPI_STORE16) {
                     tmem_ld_32x32b_x32(taddr + c * 32, raw);
                     if (lane == 0) bulk_wait_read<EPI_NBUF - 1>();
                     __syncwarp();
                     tmem_ld_wait();
-                    chunk_store16<false>(a, raw, buf, 0, lane, n, false, 1.0f);
+                    chunk_store16_any<false>(a, raw, buf, 0, lane, n);
                 } else {
                     tmem_ld_32x32b_x32(taddr + c * 32, raw);
                     if (has_res) mbar_wait(rbar(b), (nch / EPI_NBUF) & 1);       // residual box landed
                     else { if (lane == 0) bulk_wait_read<EPI_NBUF - 1>(); __syncwarp(); }
                     tmem_ld_wait();
-                    chunk_store32(a, raw, buf, lane, n, rmeta, has_res);
+                    chunk_store32_any(a, raw, buf, lane, n, gate_row, has_res);
                 }
                 fence_proxy_async();
                 __syncwarp();
@@ -596,11 +656,13 @@ template <int BN, int EPI, int EW, int NCTA> void launch_t(const gemm_args & a, 
     cfg.blockDim = dim3(C::THREADS);
     cfg.dynamicSmemBytes = C::SMEM_BYTES;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = NCTA; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = 2;
     MIO_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN, EPI, EW, NCTA>, a));
     count_launch();
 }
@@ -616,6 +678,12 @@ template <int BN, int EW, int NCTA> void launch_bn(const gemm_args & a, int num_
 }
 
 } // namespace
+
+bool pdl_enabled() {
+    static int v = -1;
+    if (v < 0) { const char * e = std::getenv("MIO_TTS_B200_PDL"); v = (e && e[0] == '0') ? 0 : 1; }
+    return v == 1;
+}
 
 int gemm_block_n(int N) { return N >= 256 ? 256 : 128; }
 int gemm_w_box_rows() { return B_BOX_ROWS; }

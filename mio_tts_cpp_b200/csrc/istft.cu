@@ -111,6 +111,7 @@ __device__ __forceinline__ void stockham_pass(const float2 * x, float2 * y, int 
 }
 
 __global__ void __launch_bounds__(ISTFT_THREADS, 1) istft_kernel(const istft_params P) {
+    MIO_PDL_PROLOGUE();
     extern __shared__ __align__(16) uint8_t smem[];
     const int N = P.n_fft, H = P.hop, M = P.M;
     const int carry_len = N - H;
@@ -265,6 +266,7 @@ __global__ void __launch_bounds__(ISTFT_THREADS, 1) istft_kernel(const istft_par
 __global__ void peak_normalize_kernel(float * __restrict__ audio, const long long * __restrict__ audio_off,
                                       const long long * __restrict__ audio_len,
                                       const unsigned int * __restrict__ peak_bits) {
+    MIO_PDL_PROLOGUE();
     const int utt = blockIdx.y;
     const double peak = (double) __uint_as_float(peak_bits[utt]);
     if (!(peak > 0.98)) return;
@@ -284,6 +286,7 @@ __device__ __forceinline__ unsigned long long splitmix64(unsigned long long x) {
 }
 
 __global__ void fill_spec_kernel(float * __restrict__ spec, long long rows, int pitch, int n_freq, unsigned long long seed) {
+    MIO_PDL_PROLOGUE();
     const long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= rows * n_freq) return;
     const long long r = i / n_freq;
@@ -299,6 +302,7 @@ __global__ void fill_spec_kernel(float * __restrict__ spec, long long rows, int 
 }
 
 __global__ void sum_kernel(const float * __restrict__ x, long long n, double * __restrict__ out) {
+    MIO_PDL_PROLOGUE();
     double acc = 0.0;
     for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x)
         acc += (double) x[i];
@@ -312,7 +316,7 @@ __global__ void sum_kernel(const float * __restrict__ x, long long n, double * _
 void launch_fill_spec(float * spec, long long rows, int pitch, int n_freq, unsigned long long seed, cudaStream_t st) {
     const long long n = rows * n_freq;
     if (n <= 0) return;
-    fill_spec_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, st>>>(spec, rows, pitch, n_freq, seed);
+    launch_pdl(fill_spec_kernel, dim3((unsigned) ((n + 255) / 256)), dim3(256), 0, st, spec, rows, pitch, n_freq, seed);
     MIO_CUDA(cudaGetLastError());
     count_launch();
 }
@@ -321,7 +325,7 @@ double device_sum(const float * x, long long n, cudaStream_t st) {
     double * d = nullptr;
     MIO_CUDA(cudaMalloc(&d, sizeof(double)));
     MIO_CUDA(cudaMemsetAsync(d, 0, sizeof(double), st));
-    sum_kernel<<<1024, 256, 0, st>>>(x, n, d);
+    launch_pdl(sum_kernel, dim3(1024), dim3(256), 0, st, x, n, d);
     MIO_CUDA(cudaGetLastError());
     count_launch();
     double h = 0.0;
@@ -418,7 +422,7 @@ void launch_istft(const istft_plan & p, const float * spec, int pitch, const int
             smem_set[dev & 63] = p.smem_bytes;
         }
     }
-    istft_kernel<<<grid, ISTFT_THREADS, p.smem_bytes, st>>>(P);
+    launch_pdl(istft_kernel, dim3(grid), dim3(ISTFT_THREADS), p.smem_bytes, st, P);
     MIO_CUDA(cudaGetLastError());
     count_launch();
 }
@@ -429,7 +433,7 @@ void launch_peak_normalize(float * audio, const long long * audio_off, const lon
     long long bx = (max_len + 256 * 8 - 1) / (256 * 8);
     if (bx > 1024) bx = 1024;
     dim3 grid((unsigned) bx, (unsigned) n_utt);
-    peak_normalize_kernel<<<grid, 256, 0, st>>>(audio, audio_off, audio_len, peak_bits);
+    launch_pdl(peak_normalize_kernel, dim3(grid), dim3(256), 0, st, audio, audio_off, audio_len, peak_bits);
     MIO_CUDA(cudaGetLastError());
     count_launch();
 }

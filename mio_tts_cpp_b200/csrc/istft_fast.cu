@@ -118,6 +118,7 @@ __device__ __forceinline__ float2 polar_fast(float logmag, float phase) {
 
 template <int N, int... RADIX>
 __global__ void __launch_bounds__(FTHREADS, 1) istft_fast_kernel(const fast_params P) {
+    MIO_PDL_PROLOGUE();
     constexpr int M = N / 2, H = N / 4, CARRY = N - H, SPAN = FW * H;
     extern __shared__ __align__(16) uint8_t smem[];
     float2 * s_twm = reinterpret_cast<float2 *>(smem);                 // [M]
@@ -264,7 +265,7 @@ void launch_fast_t(const fast_params & P, int n_utt, int max_frames, cudaStream_
     const long long n_full_max = (long long) (max_frames - 1) * H + N;
     const long long chunk = (long long) P.frames_per_chunk * H;
     dim3 grid((unsigned) ((n_full_max + chunk - 1) / chunk), (unsigned) n_utt);
-    istft_fast_kernel<N, RADIX...><<<grid, FTHREADS, smem, st>>>(P);
+    launch_pdl(istft_fast_kernel<N, RADIX...>, dim3(grid), dim3(FTHREADS), smem, st, P);
     MIO_CUDA(cudaGetLastError());
     count_launch();
 }

@@ -100,13 +100,17 @@ struct loader {
         return true;
     }
 
-    bool tblock_load(const std::string & p, int dim, int ff, tblock & blk) {
+    bool tblock_load(const std::string & p, int dim, int ff, int heads, tblock & blk) {
         std::vector<float> q, k, v, o, w1, w2, w3;
         if (!get(p + "attn_q.weight", q, (size_t) dim * dim) || !get(p + "attn_k.weight", k, (size_t) dim * dim) ||
             !get(p + "attn_v.weight", v, (size_t) dim * dim) || !get(p + "attn_output.weight", o, (size_t) dim * dim) ||
             !get(p + "ffn_gate.weight", w1, (size_t) ff * dim) || !get(p + "ffn_down.weight", w2, (size_t) dim * ff) ||
             !get(p + "ffn_up.weight", w3, (size_t) ff * dim))
             return false;
+        // softmax(q k^T * 1/sqrt(head_dim)) (src/miocodec-decoder.cpp:1251-1257): the scale is folded into Wq
+        // (exact for head_dim = 64: a power of two), so the QKV epilogue only rotates
+        const float q_scale = 1.0f / sqrtf((float) (dim / std::max(1, heads)));
+        for (float & x : q) x *= q_scale;
         std::vector<float> qkv;
         qkv.reserve(3 * q.size());
         qkv.insert(qkv.end(), q.begin(), q.end());
@@ -262,7 +266,7 @@ bool model::load(const std::string & path, int dev, std::string & err) {
     for (int i = 0; i < hp.prenet_layers; ++i) {
         const std::string p = "wave_prenet.blk." + std::to_string(i) + ".";
         if (!L.norm(p + "attn_norm", pd, prenet[i].ln1) || !L.norm(p + "ffn_norm", pd, prenet[i].ln2) ||
-            !L.tblock_load(p, pd, hp.prenet_ff, prenet[i]))
+            !L.tblock_load(p, pd, hp.prenet_ff, hp.prenet_heads, prenet[i]))
             return false;
     }
     if (!L.norm("wave_prenet.norm", pd, prenet_norm)) return false;
@@ -299,7 +303,7 @@ bool model::load(const std::string & path, int dev, std::string & err) {
     decoder.resize((size_t) hp.decoder_layers);
     for (int i = 0; i < hp.decoder_layers; ++i) {
         const std::string p = "wave_decoder.blk." + std::to_string(i) + ".";
-        if (!L.tblock_load(p, dd, hp.decoder_ff, decoder[i])) return false;
+        if (!L.tblock_load(p, dd, hp.decoder_ff, hp.decoder_heads, decoder[i])) return false;
         if (hp.dynamic_global) {
             if (!add_cond(p + "attn_cond", 3 * dd, decoder[i].cond_attn_off) ||
                 !add_cond(p + "ffn_cond", 3 * dd, decoder[i].cond_ffn_off)) {

@@ -30,6 +30,7 @@ __device__ __forceinline__ float silu_exact(float x) { return x / (1.0f + expf(-
 // ---- A1: ggml_get_rows(token_embd, codes), src/miocodec-decoder.cpp:1360.  Pure copy: bit-exact. ----------
 __global__ void gather_kernel(const float * __restrict__ table, const int * __restrict__ codes,
                               float * __restrict__ out, int n_rows, int dim) {
+    MIO_PDL_PROLOGUE();
     const int warps_per_block = blockDim.x >> 5;
     const int row = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
     if (row >= n_rows) return;
@@ -54,6 +55,7 @@ constexpr int COND_UTT = 64, COND_ROWS = 16;
 __global__ void __launch_bounds__(256) cond_kernel(const float * __restrict__ w, const float * __restrict__ b,
                                                    const float * __restrict__ emb, float * __restrict__ out, int n_out,
                                                    int adim, int n_utt) {
+    MIO_PDL_PROLOGUE();
     extern __shared__ float cond_smem[];
     float * es = cond_smem;                                  // [COND_UTT][adim + 1]
     float * ws = cond_smem + COND_UTT * (adim + 1);          // [COND_ROWS][adim]
@@ -95,6 +97,7 @@ __global__ void layernorm_kernel(const float * __restrict__ x, int rows, float e
                                  const float * __restrict__ b, const float * __restrict__ cond, int cond_ld,
                                  int shift_off, int scale_off, const int * __restrict__ row_utt, void * out16,
                                  int out_dtype, float * out32) {
+    MIO_PDL_PROLOGUE();
     constexpr int DIM = NV * 128;
     const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= rows) return;
@@ -150,6 +153,7 @@ __global__ void layernorm_generic_kernel(const float * __restrict__ x, int rows,
                                          const float * __restrict__ cond, int cond_ld, int shift_off, int scale_off,
                                          const int * __restrict__ row_utt, void * out16, int out_dtype,
                                          float * out32) {
+    MIO_PDL_PROLOGUE();
     const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= rows) return;
     const int lane = threadIdx.x & 31;
@@ -174,6 +178,7 @@ __global__ void layernorm_generic_kernel(const float * __restrict__ x, int rows,
 }
 
 __global__ void cast16_kernel(const float * __restrict__ x, void * out16, int out_dtype, size_t n4) {
+    MIO_PDL_PROLOGUE();
     const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n4) return;
     const float4 v = reinterpret_cast<const float4 *>(x)[i];
@@ -188,6 +193,7 @@ __global__ void cast16_kernel(const float * __restrict__ x, void * out16, int ou
 template <int VEC>
 __global__ void gn_stats_kernel(const float * __restrict__ x, int dim, int groups, const row_tile * __restrict__ tiles,
                                 double * __restrict__ stats) {
+    MIO_PDL_PROLOGUE();
     extern __shared__ double s_acc[];   // [groups][2]
     const row_tile t = tiles[blockIdx.x];
     for (int i = threadIdx.x; i < groups * 2; i += blockDim.x) s_acc[i] = 0.0;
@@ -221,6 +227,7 @@ __global__ void gn_stats_kernel(const float * __restrict__ x, int dim, int group
 
 __global__ void gn_finalize_kernel(const double * __restrict__ stats, const int * __restrict__ utt_len, int cpg,
                                    int groups, int n_utt, float eps, float2 * __restrict__ mr) {
+    MIO_PDL_PROLOGUE();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_utt * groups) return;
     const double n = (double) utt_len[i / groups] * (double) cpg;
@@ -236,6 +243,7 @@ __global__ void gn_apply_kernel(const float * __restrict__ x, int rows, int dim,
                                 const float2 * __restrict__ mr, const float * __restrict__ w,
                                 const float * __restrict__ b, const int * __restrict__ row_utt, void * out16,
                                 int out_dtype) {
+    MIO_PDL_PROLOGUE();
     const int c4n = dim >> 2;
     const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (size_t) rows * c4n) return;
@@ -270,6 +278,7 @@ __global__ void gn_apply_fast_kernel(const float * __restrict__ x, int rows, int
                                      const float2 * __restrict__ mr, const float * __restrict__ w,
                                      const float * __restrict__ b, const int * __restrict__ row_utt, void * out16,
                                      int out_dtype) {
+    MIO_PDL_PROLOGUE();
     const int c4n = dim >> 2;
     const int rpb = blockDim.x / c4n;                 // rows per block pass
     const int c4 = threadIdx.x % c4n;
@@ -313,6 +322,7 @@ __global__ void interp_kernel(const float * __restrict__ src, const int * __rest
                               const int * __restrict__ src_len, float * __restrict__ dst, int rows, int dim,
                               const int * __restrict__ row_utt, const int * __restrict__ row_pos,
                               const int * __restrict__ utt_len) {
+    MIO_PDL_PROLOGUE();
     const int c4n = dim >> 2;
     const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (size_t) rows * c4n) return;
@@ -345,6 +355,7 @@ __global__ void interp_kernel(const float * __restrict__ src, const int * __rest
 
 // ---- RoPE cache: theta_i = pos * s^i by repeated fp32 multiplication (ggml-cpu/ops.cpp:5616-5625) ----
 __global__ void rope_table_kernel(float2 * __restrict__ table, int n_pos, int half_dim, float theta_scale) {
+    MIO_PDL_PROLOGUE();
     const int pos = blockIdx.x * blockDim.x + threadIdx.x;
     if (pos >= n_pos) return;
     float theta = (float) pos;
@@ -361,6 +372,7 @@ __global__ void convt_fold_snake_kernel(const float * __restrict__ y, int ld_y, 
                                         int ksize, int stride, int pad, const float * __restrict__ bias,
                                         const float * __restrict__ snake_a, const float * __restrict__ snake_inv_b,
                                         const int * __restrict__ row_utt, const int * __restrict__ row_pos) {
+    MIO_PDL_PROLOGUE();
     const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (size_t) rows * cout) return;
     const int row = (int) (i / cout);
@@ -388,6 +400,7 @@ __global__ void convt_fold_snake_kernel(const float * __restrict__ y, int ld_y, 
 
 __global__ void snake_kernel(float * __restrict__ x, int rows, int dim, const float * __restrict__ snake_a,
                              const float * __restrict__ snake_inv_b) {
+    MIO_PDL_PROLOGUE();
     const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (size_t) rows * dim) return;
     const int c = (int) (i % dim);
@@ -402,7 +415,7 @@ inline unsigned blocks_for(size_t n, int threads) { return (unsigned) ((n + thre
 
 void launch_gather(const float * table, const int * codes, float * out, int n_rows, int dim, cudaStream_t st) {
     if (n_rows <= 0) return;
-    gather_kernel<<<blocks_for((size_t) n_rows, 8), 256, 0, st>>>(table, codes, out, n_rows, dim);
+    launch_pdl(gather_kernel, dim3(blocks_for((size_t) n_rows, 8)), dim3(256), 0, st, table, codes, out, n_rows, dim);
     MIO_CUDA(cudaGetLastError());
     count_launch();
 }
@@ -420,7 +433,7 @@ void launch_cond(const float * w, const float * b, const float * emb, float * ou
         MIO_CUDA(cudaFuncSetAttribute(cond_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         configured[dev & 63] = true;
     }
-    cond_kernel<<<grid, 256, smem, st>>>(w, b, emb, out, n_out, adim, n_utt);
+    launch_pdl(cond_kernel, dim3(grid), dim3(256), smem, st, w, b, emb, out, n_out, adim, n_utt);
     MIO_CUDA(cudaGetLastError());
     count_launch();
 }
@@ -432,7 +445,7 @@ void launch_layernorm(const float * x, int rows, int dim, float eps, const float
     const unsigned grid = blocks_for((size_t) rows, 8);
 #define LN_CASE(NV)                                                                                              \
     case NV:                                                                                                     \
-        layernorm_kernel<NV><<<grid, 256, 0, st>>>(x, rows, eps, w, b, cond, cond_ld, shift_off, scale_off,      \
+        launch_pdl(layernorm_kernel<NV>, dim3(grid), dim3(256), 0, st, x, rows, eps, w, b, cond, cond_ld, shift_off, scale_off,      \
                                                    row_utt, out16, out_dtype, out32);                            \
         break;
     if ((dim % 128) == 0 && dim <= 1024 && (!cond || ((cond_ld | shift_off | scale_off) & 3) == 0)) {
@@ -440,7 +453,7 @@ void launch_layernorm(const float * x, int rows, int dim, float eps, const float
             LN_CASE(1) LN_CASE(2) LN_CASE(3) LN_CASE(4) LN_CASE(5) LN_CASE(6) LN_CASE(7) LN_CASE(8)
         }
     } else {
-        layernorm_generic_kernel<<<grid, 256, 0, st>>>(x, rows, dim, eps, w, b, cond, cond_ld, shift_off, scale_off,
+        launch_pdl(layernorm_generic_kernel, dim3(grid), dim3(256), 0, st, x, rows, dim, eps, w, b, cond, cond_ld, shift_off, scale_off,
                                                        row_utt, out16, out_dtype, out32);
     }
 #undef LN_CASE
@@ -451,7 +464,7 @@ void launch_layernorm(const float * x, int rows, int dim, float eps, const float
 void launch_cast16(const float * x, void * out16, int out_dtype, size_t n, cudaStream_t st) {
     if (n == 0) return;
     if (n & 3) throw cuda_error("cast16: element count must be a multiple of 4");
-    cast16_kernel<<<blocks_for(n >> 2, 256), 256, 0, st>>>(x, out16, out_dtype, n >> 2);
+    launch_pdl(cast16_kernel, dim3(blocks_for(n >> 2, 256)), dim3(256), 0, st, x, out16, out_dtype, n >> 2);
     MIO_CUDA(cudaGetLastError());
     count_launch();
 }
@@ -464,10 +477,10 @@ void launch_gn_stats(const float * x, int dim, int groups, const row_tile * tile
     if ((cpg & 3) == 0) {
         const int cols = dim / 4;
         const int threads = cols >= 256 ? ((cols + 31) / 32) * 32 : 256;
-        gn_stats_kernel<4><<<n_tiles, threads > 1024 ? 1024 : threads, smem, st>>>(x, dim, groups, tiles, stats);
+        launch_pdl(gn_stats_kernel<4>, dim3(n_tiles), dim3(threads > 1024 ? 1024 : threads), smem, st, x, dim, groups, tiles, stats);
     } else {
         const int threads = dim >= 256 ? ((dim + 31) / 32) * 32 : 256;
-        gn_stats_kernel<1><<<n_tiles, threads > 1024 ? 1024 : threads, smem, st>>>(x, dim, groups, tiles, stats);
+        launch_pdl(gn_stats_kernel<1>, dim3(n_tiles), dim3(threads > 1024 ? 1024 : threads), smem, st, x, dim, groups, tiles, stats);
     }
     MIO_CUDA(cudaGetLastError());
     count_launch();
@@ -481,10 +494,10 @@ void launch_gn_apply(const float * x, int rows, int dim, int groups, const float
     if ((cpg & 3) == 0 && c4n <= 256 && (256 % c4n) == 0) {
         constexpr int RPT = 4;
         const int rows_per_block = (256 / c4n) * RPT;
-        gn_apply_fast_kernel<RPT><<<blocks_for((size_t) rows, rows_per_block), 256, 0, st>>>(
+        launch_pdl(gn_apply_fast_kernel<RPT>, dim3(blocks_for((size_t) rows, rows_per_block)), dim3(256), 0, st, 
             x, rows, dim, groups, mean_rstd, w, b, row_utt, out16, out_dtype);
     } else {
-        gn_apply_kernel<<<blocks_for((size_t) rows * (dim >> 2), 256), 256, 0, st>>>(
+        launch_pdl(gn_apply_kernel, dim3(blocks_for((size_t) rows * (dim >> 2), 256)), dim3(256), 0, st, 
             x, rows, dim, groups, mean_rstd, w, b, row_utt, out16, out_dtype);
     }
     MIO_CUDA(cudaGetLastError());
@@ -493,7 +506,7 @@ void launch_gn_apply(const float * x, int rows, int dim, int groups, const float
 
 void launch_gn_finalize(const double * stats, const int * utt_len, int cpg, int groups, int n_utt, float eps,
                         float2 * mr, cudaStream_t st) {
-    gn_finalize_kernel<<<blocks_for((size_t) n_utt * groups, 128), 128, 0, st>>>(stats, utt_len, cpg, groups, n_utt,
+    launch_pdl(gn_finalize_kernel, dim3(blocks_for((size_t) n_utt * groups, 128)), dim3(128), 0, st, stats, utt_len, cpg, groups, n_utt,
                                                                                eps, mr);
     MIO_CUDA(cudaGetLastError());
     count_launch();
@@ -503,7 +516,7 @@ void launch_interp(const float * src, const int * src_row0, const int * src_len,
                    const int * row_utt, const int * row_pos, const int * utt_len, cudaStream_t st) {
     if (rows <= 0) return;
     if (dim & 3) throw cuda_error("interp: channel count must be a multiple of 4");
-    interp_kernel<<<blocks_for((size_t) rows * (dim >> 2), 256), 256, 0, st>>>(src, src_row0, src_len, dst, rows, dim,
+    launch_pdl(interp_kernel, dim3(blocks_for((size_t) rows * (dim >> 2), 256)), dim3(256), 0, st, src, src_row0, src_len, dst, rows, dim,
                                                                                row_utt, row_pos, utt_len);
     MIO_CUDA(cudaGetLastError());
     count_launch();
@@ -511,7 +524,7 @@ void launch_interp(const float * src, const int * src_row0, const int * src_len,
 
 void launch_rope_table(float2 * table, int n_pos, int half_dim, float theta_scale, cudaStream_t st) {
     if (n_pos <= 0) return;
-    rope_table_kernel<<<blocks_for((size_t) n_pos, 128), 128, 0, st>>>(table, n_pos, half_dim, theta_scale);
+    launch_pdl(rope_table_kernel, dim3(blocks_for((size_t) n_pos, 128)), dim3(128), 0, st, table, n_pos, half_dim, theta_scale);
     MIO_CUDA(cudaGetLastError());
     count_launch();
 }
@@ -521,7 +534,7 @@ void launch_convt_fold_snake(const float * y, int ld_y, const int * src_row0, co
                              const float * snake_a, const float * snake_inv_b, const int * row_utt,
                              const int * row_pos, cudaStream_t st) {
     if (rows <= 0) return;
-    convt_fold_snake_kernel<<<blocks_for((size_t) rows * cout, 256), 256, 0, st>>>(
+    launch_pdl(convt_fold_snake_kernel, dim3(blocks_for((size_t) rows * cout, 256)), dim3(256), 0, st, 
         y, ld_y, src_row0, src_len, dst, rows, cout, ksize, stride, pad, bias, snake_a, snake_inv_b, row_utt, row_pos);
     MIO_CUDA(cudaGetLastError());
     count_launch();
@@ -529,7 +542,7 @@ void launch_convt_fold_snake(const float * y, int ld_y, const int * src_row0, co
 
 void launch_snake(float * x, int rows, int dim, const float * snake_a, const float * snake_inv_b, cudaStream_t st) {
     if (rows <= 0) return;
-    snake_kernel<<<blocks_for((size_t) rows * dim, 256), 256, 0, st>>>(x, rows, dim, snake_a, snake_inv_b);
+    launch_pdl(snake_kernel, dim3(blocks_for((size_t) rows * dim, 256)), dim3(256), 0, st, x, rows, dim, snake_a, snake_inv_b);
     MIO_CUDA(cudaGetLastError());
     count_launch();
 }
