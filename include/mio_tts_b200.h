@@ -190,6 +190,25 @@ MIO_B200_API uint64_t mio_tts_b200_resident_samples(struct mio_tts_context * ctx
 MIO_B200_API float mio_tts_b200_istft_bench(struct mio_tts_context * ctx, int32_t n_utt, int32_t frames_per_utt,
                                             int32_t n_fft, int32_t hop, int32_t iters, uint64_t seed, double * checksum,
                                             char * err, size_t err_size);
+/* ---- reference-audio -> speaker-embedding path (WavLM SSL extractor + global encoder) ----
+ * mio_tts_reference_to_embedding (lib.h:69-77, lib.cpp:1048-1125) runs on the GPU when the context was created with a
+ * WavLM GGUF and the MioCodec GGUF holds the global-encoder tensors.  The reference has no batch or PCM entry point:
+ * `pcm[i]` = `n_samples[i]` mono float samples at `sample_rate` (what miniaudio hands wavlm_extractor, wavlm-extractor.cpp
+ * :153-203); embedding_out[i] is malloc'd ([output_channels] floats) and released with mio_tts_embedding_free. */
+MIO_B200_API bool mio_tts_b200_reference_pcm_to_embedding_batch(struct mio_tts_context * ctx, const float * const * pcm,
+                                                                const size_t * n_samples, int32_t sample_rate, size_t batch,
+                                                                struct mio_tts_params params, float ** embedding_out,
+                                                                size_t * n_embedding_out, char * err, size_t err_size);
+/* parity hooks: wavlm_extractor::extract_ssl_features (wavlm-extractor.cpp:543) on PCM -> malloc'd [n_frames][dim];
+ * miocodec_decoder::encode_global_embedding_from_ssl (miocodec-decoder.cpp:824) on [n_frames][channels] features */
+MIO_B200_API bool mio_tts_b200_extract_ssl(struct mio_tts_context * ctx, const float * pcm, size_t n_samples, int32_t sample_rate,
+                                           float max_reference_seconds, float ** ssl_out, int32_t * n_frames_out,
+                                           int32_t * dim_out, char * err, size_t err_size);
+MIO_B200_API bool mio_tts_b200_ssl_to_embedding(struct mio_tts_context * ctx, const float * ssl, int32_t n_frames, int32_t channels,
+                                                float ** embedding_out, size_t * n_embedding_out, char * err, size_t err_size);
+/* BASELINE config 4: `batch` copies of one clip resident in HBM, `iters` passes; returns ms per batch (<0 on error) */
+MIO_B200_API float mio_tts_b200_reference_bench(struct mio_tts_context * ctx, const float * pcm, size_t n_samples,
+                                                int32_t sample_rate, int32_t batch, int32_t iters, char * err, size_t err_size);
 /* number of this library's kernels launched so far in this process */
 MIO_B200_API uint64_t mio_tts_b200_launch_count(void);
 MIO_B200_API uint64_t mio_tts_b200_workspace_bytes(struct mio_tts_context * ctx);

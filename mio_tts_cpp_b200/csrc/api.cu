@@ -5,6 +5,7 @@
 
 #include "engine.h"
 #include "gguf_io.h"
+#include "refenc.h"
 
 #include <dlfcn.h>
 
@@ -24,6 +25,8 @@ using namespace mio;
 struct mio_tts_context {
     std::shared_ptr<model> mdl;
     std::unique_ptr<engine> eng;
+    std::shared_ptr<refmodel> ref;      // WavLM + global-encoder weights (reference-audio path), shared by clones
+    std::unique_ptr<refenc> renc;       // per-context stream + workspace of that path
     std::string vocoder_path, wavlm_path;
 };
 
@@ -75,6 +78,77 @@ std::shared_ptr<model> load_model(const std::string & path, int device, std::str
     auto m = std::make_shared<model>();
     if (!m->load(path, device, err)) return nullptr;
     return m;
+}
+
+// WavLM GGUF (optional) + the global-encoder tensors of the MioCodec GGUF (optional), lib.cpp:833-840
+std::shared_ptr<refmodel> load_refmodel(const std::string & vocoder_path, const std::string & wavlm_path, int device, int out_dim,
+                                        std::string & err) {
+    auto r = std::make_shared<refmodel>();
+    {
+        gguf_file g;
+        std::string e;
+        if (!g.load(vocoder_path, e)) { err = "failed to load MioCodec GGUF: " + e; return nullptr; }
+        if (!r->load_global_encoder(g, device, out_dim, e)) { err = "failed to load MioCodec GGUF: " + e; return nullptr; }
+    }
+    if (!wavlm_path.empty()) {
+        std::string e;
+        if (!r->load_wavlm(wavlm_path, device, e)) { err = "failed to load WavLM GGUF: " + e; return nullptr; }
+    }
+    return r;
+}
+
+// PCM WAV file -> mono float32 (stereo averaged) + sample rate.  The reference decodes through miniaudio
+// (/root/reference/src/wavlm-extractor.cpp:153-203), which also reads MP3/FLAC and resamples to the codec rate; this
+// library reads RIFF/WAVE PCM 16/24/32-bit and float32 and resamples other rates linearly.
+bool read_wav_mono(const std::string & path, std::vector<float> & out, int & sample_rate, std::string & err) {
+    std::ifstream f(path, std::ios::binary);
+    if (!f) { err = "ma_decoder_init_file failed"; return false; }
+    std::vector<uint8_t> d((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
+    if (d.size() < 12 || std::memcmp(d.data(), "RIFF", 4) != 0 || std::memcmp(d.data() + 8, "WAVE", 4) != 0) {
+        err = "ma_decoder_init_file failed (only RIFF/WAVE PCM is supported by the B200 library)";
+        return false;
+    }
+    auto u16 = [&](size_t o) { return (uint32_t) d[o] | ((uint32_t) d[o + 1] << 8); };
+    auto u32 = [&](size_t o) { return u16(o) | (u16(o + 2) << 16); };
+    size_t pos = 12, data_off = 0, data_len = 0;
+    uint32_t tag = 0, ch = 0, sr = 0, bits = 0;
+    while (pos + 8 <= d.size()) {
+        const uint32_t size = u32(pos + 4);
+        const size_t body = pos + 8;
+        if (std::memcmp(d.data() + pos, "fmt ", 4) == 0 && body + 16 <= d.size()) {
+            tag = u16(body); ch = u16(body + 2); sr = u32(body + 4); bits = u16(body + 14);
+            if (tag == 0xFFFE && size >= 26 && body + 26 <= d.size()) tag = u16(body + 24);   // WAVE_FORMAT_EXTENSIBLE
+        } else if (std::memcmp(d.data() + pos, "data", 4) == 0) {
+            data_off = body;
+            data_len = std::min<size_t>(size, d.size() - body);
+        }
+        pos = body + size + (size & 1);
+    }
+    if (ch == 0 || sr == 0 || data_off == 0) { err = "ma_decoder_init_file failed (no fmt/data chunk)"; return false; }
+    const size_t bps = bits / 8;
+    if (!((tag == 1 && (bits == 16 || bits == 24 || bits == 32)) || (tag == 3 && bits == 32))) {
+        err = "ma_decoder_init_file failed (unsupported WAV sample format)";
+        return false;
+    }
+    const size_t frames = data_len / (bps * ch);
+    if (frames == 0) { err = "ma_decoder_get_length_in_pcm_frames failed"; return false; }
+    out.resize(frames);
+    const uint8_t * p = d.data() + data_off;
+    for (size_t i = 0; i < frames; ++i) {
+        float acc = 0.0f;
+        for (uint32_t c = 0; c < ch; ++c) {
+            const uint8_t * q = p + (i * ch + c) * bps;
+            float v;
+            if (tag == 3) { std::memcpy(&v, q, 4); }
+            else if (bits == 16) { v = (float) (int16_t) (q[0] | (q[1] << 8)) / 32768.0f; }
+            else if (bits == 24) { v = (float) ((int32_t) ((uint32_t) q[0] << 8 | (uint32_t) q[1] << 16 | (uint32_t) q[2] << 24) >> 8) / 8388608.0f; }
+            else { int32_t t; std::memcpy(&t, q, 4); v = (float) ((double) t / 2147483648.0); }
+            acc += v;
+        }
+        out[i] = ch > 1 ? acc / (float) ch : acc;
+    }
+    sample_rate = (int) sr;
+    return true;
 }
 
 // ---- text codes (lib.cpp:71-113, 225-286) ----
@@ -176,11 +250,16 @@ struct mio_tts_context * mio_tts_init_from_file(const char * model_vocoder, cons
         std::string load_err;
         auto m = load_model(model_vocoder, default_device(), load_err);
         if (!m) throw std::runtime_error("failed to load MioCodec GGUF: " + load_err);
+        const std::string wavlm = (wavlm_model != nullptr && wavlm_model[0] != '\0') ? wavlm_model : "";
+        auto r = load_refmodel(model_vocoder, wavlm, m->device, m->hp.decoder_adanorm_dim, load_err);
+        if (!r) throw std::runtime_error(load_err);
         ctx = new mio_tts_context();
         ctx->mdl = m;
         ctx->eng.reset(new engine(m));
+        ctx->ref = r;
+        ctx->renc.reset(new refenc(r));
         ctx->vocoder_path = model_vocoder;
-        if (wavlm_model != nullptr && wavlm_model[0] != '\0') ctx->wavlm_path = wavlm_model;
+        ctx->wavlm_path = wavlm;
     });
     if (!ok) { delete ctx; return nullptr; }
     return ctx;
@@ -196,6 +275,8 @@ struct mio_tts_context * mio_tts_context_clone(const struct mio_tts_context * ct
         out = new mio_tts_context();
         out->mdl = ctx->mdl;
         out->eng.reset(new engine(ctx->mdl));
+        out->ref = ctx->ref;
+        if (ctx->ref) out->renc.reset(new refenc(ctx->ref));
         out->vocoder_path = ctx->vocoder_path;
         out->wavlm_path = ctx->wavlm_path;
     });
@@ -239,9 +320,14 @@ bool mio_tts_context_set_backend_device(struct mio_tts_context * ctx, const char
         std::string load_err;
         auto m = load_model(ctx->vocoder_path, dev, load_err);
         if (!m) throw std::runtime_error("decoder backend setup failed: " + load_err);
+        auto r = load_refmodel(ctx->vocoder_path, ctx->wavlm_path, dev, m->hp.decoder_adanorm_dim, load_err);
+        if (!r) throw std::runtime_error("wavlm backend setup failed: " + load_err);
         ctx->eng.reset();
+        ctx->renc.reset();
         ctx->mdl = m;
+        ctx->ref = r;
         ctx->eng.reset(new engine(m));
+        ctx->renc.reset(new refenc(r));
     });
 }
 
@@ -347,15 +433,137 @@ bool mio_tts_codes_save(const char * path, const int32_t * codes, size_t n_codes
 
 void mio_tts_codes_free(int32_t * codes) { std::free(codes); }
 
-bool mio_tts_reference_to_embedding(struct mio_tts_context * ctx, const char * reference_audio, struct mio_tts_params,
+// checks of mio_tts_reference_to_embedding, lib.cpp:1056-1083, in the reference's order
+static bool reference_checks(struct mio_tts_context * ctx, char * err, size_t err_size) {
+    if (!ctx->mdl->hp.dynamic_global) { set_err(err, err_size, "reference embedding requires dynamic-global MioCodec"); return false; }
+    if (!ctx->ref || !ctx->ref->has_global_encoder()) {
+        set_err(err, err_size, "reference embedding requires global_encoder tensors in MioCodec GGUF");
+        return false;
+    }
+    if (ctx->wavlm_path.empty() || !ctx->ref->has_wavlm()) { set_err(err, err_size, "WavLM model is not loaded"); return false; }
+    return true;
+}
+
+bool mio_tts_b200_reference_pcm_to_embedding_batch(struct mio_tts_context * ctx, const float * const * pcm, const size_t * n_samples,
+                                                   int32_t sample_rate, size_t batch, struct mio_tts_params params,
+                                                   float ** embedding_out, size_t * n_embedding_out, char * err, size_t err_size) {
+    if (ctx == nullptr || !ctx->mdl) { set_err(err, err_size, "context is null"); return false; }
+    if (pcm == nullptr || n_samples == nullptr || batch == 0) { set_err(err, err_size, "reference audio is empty"); return false; }
+    if (embedding_out == nullptr || n_embedding_out == nullptr) { set_err(err, err_size, "output pointers are null"); return false; }
+    if (!reference_checks(ctx, err, err_size)) return false;
+    std::vector<float *> bufs(batch, nullptr);
+    const bool ok = guarded(err, err_size, [&] {
+        std::lock_guard<std::mutex> lk(ctx->renc->mtx);
+        refenc & R = *ctx->renc;
+        try {
+            R.prepare(pcm, n_samples, sample_rate, params.max_reference_seconds, batch);
+            R.run_wavlm();
+        } catch (const std::exception & e) {
+            throw std::runtime_error(std::string("failed to extract WavLM SSL features: ") + e.what());
+        }
+        try {
+            R.run_global();
+        } catch (const std::exception & e) {
+            throw std::runtime_error(std::string("failed to encode global embedding: ") + e.what());
+        }
+        const size_t n_out = (size_t) ctx->ref->ge_out;
+        for (size_t c = 0; c < batch; ++c) {
+            bufs[c] = (float *) std::malloc(n_out * sizeof(float));      // lib.cpp:1115, freed by mio_tts_embedding_free
+            if (bufs[c] == nullptr) throw std::runtime_error("failed to allocate output embedding");
+            R.fetch_embedding(c, bufs[c]);
+        }
+        R.sync();
+        for (size_t c = 0; c < batch; ++c) { embedding_out[c] = bufs[c]; n_embedding_out[c] = n_out; }
+    });
+    if (!ok) {
+        try { ctx->renc->sync(); } catch (...) {}
+        for (float * p : bufs) std::free(p);
+    }
+    return ok;
+}
+
+bool mio_tts_reference_to_embedding(struct mio_tts_context * ctx, const char * reference_audio, struct mio_tts_params params,
                                     float ** embedding_out, size_t * n_embedding_out, char * err, size_t err_size) {
     if (ctx == nullptr || !ctx->mdl) { set_err(err, err_size, "context is null"); return false; }
     if (reference_audio == nullptr || reference_audio[0] == '\0') { set_err(err, err_size, "reference_audio path is empty"); return false; }
     if (embedding_out == nullptr || n_embedding_out == nullptr) { set_err(err, err_size, "output pointers are null"); return false; }
-    if (!ctx->mdl->hp.dynamic_global) { set_err(err, err_size, "reference embedding requires dynamic-global MioCodec"); return false; }
-    // WavLM + global encoder are not part of the decode path this library accelerates
-    set_err(err, err_size, "WavLM model is not loaded");
-    return false;
+    if (!reference_checks(ctx, err, err_size)) return false;
+    std::vector<float> pcm;
+    int sr = 0;
+    std::string e;
+    if (!read_wav_mono(reference_audio, pcm, sr, e)) {
+        set_err(err, err_size, "failed to extract WavLM SSL features: failed to decode reference audio: " + e);
+        return false;
+    }
+    // the reference asks miniaudio for the codec sample rate, then resamples to WavLM's 16 kHz itself; a file at
+    // another rate goes through one linear resampling here (wavlm-extractor.cpp:218-240) instead of miniaudio's filter
+    const float * p = pcm.data();
+    const size_t n = pcm.size();
+    return mio_tts_b200_reference_pcm_to_embedding_batch(ctx, &p, &n, sr, 1, params, embedding_out, n_embedding_out, err, err_size);
+}
+
+// parity hooks: WavLM features of PCM clips, and the global encoder alone on caller-supplied features
+bool mio_tts_b200_extract_ssl(struct mio_tts_context * ctx, const float * pcm, size_t n_samples, int32_t sample_rate,
+                              float max_reference_seconds, float ** ssl_out, int32_t * n_frames_out, int32_t * dim_out, char * err,
+                              size_t err_size) {
+    if (ctx == nullptr || !ctx->mdl) { set_err(err, err_size, "context is null"); return false; }
+    if (ssl_out == nullptr || n_frames_out == nullptr || dim_out == nullptr) { set_err(err, err_size, "output pointers are null"); return false; }
+    if (!ctx->ref || !ctx->ref->has_wavlm()) { set_err(err, err_size, "WavLM model is not loaded"); return false; }
+    float * buf = nullptr;
+    const bool ok = guarded(err, err_size, [&] {
+        std::lock_guard<std::mutex> lk(ctx->renc->mtx);
+        refenc & R = *ctx->renc;
+        R.prepare(&pcm, &n_samples, sample_rate, max_reference_seconds, 1);
+        R.run_wavlm();
+        const size_t n = (size_t) R.frames(0) * ctx->ref->hp.embed_dim;
+        buf = (float *) std::malloc(std::max<size_t>(n, 1) * sizeof(float));
+        if (buf == nullptr) throw std::runtime_error("failed to allocate ssl features");
+        R.fetch_ssl(0, buf);
+        R.sync();
+        *ssl_out = buf; *n_frames_out = R.frames(0); *dim_out = ctx->ref->hp.embed_dim;
+    });
+    if (!ok) std::free(buf);
+    return ok;
+}
+
+bool mio_tts_b200_ssl_to_embedding(struct mio_tts_context * ctx, const float * ssl, int32_t n_frames, int32_t channels,
+                                   float ** embedding_out, size_t * n_embedding_out, char * err, size_t err_size) {
+    if (ctx == nullptr || !ctx->mdl) { set_err(err, err_size, "context is null"); return false; }
+    if (embedding_out == nullptr || n_embedding_out == nullptr) { set_err(err, err_size, "output pointers are null"); return false; }
+    if (!ctx->ref || !ctx->ref->has_global_encoder()) { set_err(err, err_size, "global encoder tensors are not available in this GGUF"); return false; }
+    if (ssl == nullptr || n_frames <= 0) { set_err(err, err_size, "invalid ssl frame length"); return false; }
+    if (channels != ctx->ref->ge_in) { set_err(err, err_size, "ssl feature shape mismatch"); return false; }
+    float * buf = nullptr;
+    const bool ok = guarded(err, err_size, [&] {
+        std::lock_guard<std::mutex> lk(ctx->renc->mtx);
+        refenc & R = *ctx->renc;
+        const int fr = n_frames;
+        R.prepare_ssl(&ssl, &fr, 1);
+        R.run_global();
+        buf = (float *) std::malloc((size_t) ctx->ref->ge_out * sizeof(float));
+        if (buf == nullptr) throw std::runtime_error("failed to allocate output embedding");
+        R.fetch_embedding(0, buf);
+        R.sync();
+        *embedding_out = buf; *n_embedding_out = (size_t) ctx->ref->ge_out;
+    });
+    if (!ok) std::free(buf);
+    return ok;
+}
+
+// resident timing of the reference path: `batch` copies of one clip, `iters` passes, milliseconds per batch
+float mio_tts_b200_reference_bench(struct mio_tts_context * ctx, const float * pcm, size_t n_samples, int32_t sample_rate,
+                                   int32_t batch, int32_t iters, char * err, size_t err_size) {
+    if (ctx == nullptr || !ctx->mdl) { set_err(err, err_size, "context is null"); return -1.0f; }
+    if (!reference_checks(ctx, err, err_size)) return -1.0f;
+    float ms = -1.0f;
+    guarded(err, err_size, [&] {
+        std::lock_guard<std::mutex> lk(ctx->renc->mtx);
+        std::vector<const float *> pp((size_t) std::max(1, batch), pcm);
+        std::vector<size_t> nn((size_t) std::max(1, batch), n_samples);
+        ctx->renc->prepare(pp.data(), nn.data(), sample_rate, 0.0f, pp.size());
+        ms = ctx->renc->timed(std::max(1, iters), true);
+    });
+    return ms;
 }
 
 bool mio_tts_embedding_load_gguf(const char * path, float ** embedding_out, size_t * n_embedding_out, char * err,
@@ -492,18 +700,49 @@ bool mio_tts_estimate_workspace_bytes(struct mio_tts_context * ctx, int32_t n_co
     return true;
 }
 
-bool mio_tts_reserve_reference_workspace(struct mio_tts_context * ctx, float, char * err, size_t err_size) {
-    if (ctx == nullptr || !ctx->mdl) { set_err(err, err_size, "context is null"); return false; }
-    set_err(err, err_size, "WavLM model is not loaded");
-    return false;
+// wavlm_conv_stack_out_len over llround(rate * seconds) source samples (wavlm-extractor.cpp:242-255, 331-340)
+static long long reference_samples(const struct mio_tts_context * ctx, float max_reference_seconds) {
+    const int sr = std::max(1, ctx->mdl->hp.sample_rate);
+    const float sec = max_reference_seconds > 0.0f ? max_reference_seconds : 20.0f;   // lib.cpp:1388
+    return std::max<long long>(1, std::llround((double) sr * (double) sec));
 }
 
-bool mio_tts_estimate_reference_workspace_bytes(struct mio_tts_context * ctx, float, uint64_t * out_bytes, char * err,
-                                                size_t err_size) {
+bool mio_tts_reserve_reference_workspace(struct mio_tts_context * ctx, float max_reference_seconds, char * err, size_t err_size) {
+    if (ctx == nullptr || !ctx->mdl) { set_err(err, err_size, "context is null"); return false; }
+    if (ctx->wavlm_path.empty() || !ctx->ref || !ctx->ref->has_wavlm()) { set_err(err, err_size, "WavLM model is not loaded"); return false; }
+    if (!ctx->ref->has_global_encoder()) { set_err(err, err_size, "global encoder tensors are not available in this GGUF"); return false; }
+    const size_t n = (size_t) reference_samples(ctx, max_reference_seconds);
+    if (!guarded(err, err_size, [&] {
+            std::lock_guard<std::mutex> lk(ctx->renc->mtx);
+            std::vector<float> z(n, 0.0f);
+            const float * p = z.data();
+            ctx->renc->prepare(&p, &n, ctx->mdl->hp.sample_rate, 0.0f, 1);   // sizes every buffer for this length
+            ctx->renc->sync();
+        })) {
+        set_err(err, err_size, "failed to reserve reference workspace");
+        return false;
+    }
+    return true;
+}
+
+bool mio_tts_estimate_reference_workspace_bytes(struct mio_tts_context * ctx, float max_reference_seconds, uint64_t * out_bytes,
+                                                char * err, size_t err_size) {
     if (ctx == nullptr || !ctx->mdl) { set_err(err, err_size, "context is null"); return false; }
     if (out_bytes == nullptr) { set_err(err, err_size, "out_bytes is null"); return false; }
-    set_err(err, err_size, "WavLM model is not loaded");
-    return false;
+    if (ctx->wavlm_path.empty() || !ctx->ref || !ctx->ref->has_wavlm()) { set_err(err, err_size, "WavLM model is not loaded"); return false; }
+    if (!ctx->ref->has_global_encoder()) { set_err(err, err_size, "global encoder tensors are not available in this GGUF"); return false; }
+    // closed form of what refenc::prepare allocates for one clip (no seq^2 attention term, unlike
+    // wavlm_extractor::estimate_workspace_bytes, wavlm-extractor.cpp:342-372)
+    const refmodel & M = *ctx->ref;
+    const uint64_t n_src = (uint64_t) reference_samples(ctx, max_reference_seconds);
+    const uint64_t n_wav = std::max<uint64_t>(1, (uint64_t) std::llround((double) n_src * (double) M.hp.sample_rate / (double) std::max(1, ctx->mdl->hp.sample_rate)));
+    const uint64_t l0 = n_wav / (uint64_t) std::max(1, M.hp.conv_stride[0]) + 256;
+    const uint64_t seq = l0 / 64 + 192;
+    uint64_t b = (n_src + n_wav) * 4 + l0 * (uint64_t) M.conv_ch * 2 * 2 + (l0 / 128 + 1) * (uint64_t) M.conv_ch * 16;
+    b += seq * ((uint64_t) M.hp.embed_dim * (4 + 4 + 2 + 2 + 6 + 2 + 4) + (uint64_t) M.ffn * 2);
+    b += seq * ((uint64_t) M.ge_dim * 8 + (uint64_t) std::max(M.ge_dim, M.ge_ff) * 4);
+    *out_bytes = b + b / 8 + (32ull << 20);
+    return true;
 }
 
 bool mio_tts_audio_save_wav16(const char * path, const float * audio, size_t n_audio, int32_t sample_rate, char * err,

@@ -80,15 +80,21 @@ struct gemm_args {
     CUtensorMap map_a;       // A: [rows, K] 16-bit, box 64 x 128, swizzle 128B
     CUtensorMap map_b;       // W: [N, taps*K] 16-bit, box 64 x gemm_w_box_rows(), swizzle 128B
     CUtensorMap map_out;     // output (and in-place residual): box 32 x 32, swizzle 128B (fp32) / 64B (16-bit)
-    int M, N, K, taps;
+    int M, N, K, taps;       // K = reduction length PER TAP; W column of (tap, k) = tap*K + k
+    // A coordinates of tap t:  row = tile row + tap_row0 + (t >> tap_shift),  column = a_col0 + (t & ((1<<tap_shift)-1)) * K.
+    //   plain GEMM: taps 1.  k=3 "same" conv: tap_row0 -1.  stride-2 conv over the PAIR view [rows/2, 2C] of the input:
+    //   tap_shift 1 (taps 0,1 = the two frames of pair row r, tap 2 = first frame of pair row r+1).  grouped conv:
+    //   a_col0 = first input channel of the group, tap_row0 = -padding.
+    int tap_row0, tap_shift, a_col0;
+    int act;                 // activation after bias: 0 none, 1 GELU (ggml: tanh form through fp16), 2 tanh
     int dtype;               // op16 of A and W
     int out_dtype;           // op16 of a 16-bit output
     int epilogue;
     void * out; int ldo;
     const float * bias;
     const float * res; int ldr;          // fp32 residual: nullptr or == out (read through map_out)
-    const float * gate; int gate_ld;     // gate[utt * gate_ld + n]
-    const int * row_utt;                 // row -> utterance (needed with gate)
+    const float * gate; int gate_ld;     // gate[utt * gate_ld + n]  (gate_ld 0: one per-column scale for all rows)
+    const int * row_utt;                 // row -> utterance (needed with gate_ld != 0)
     const int * row_pos;                 // row -> position in utterance (needed with rope)
     const float2 * rope;                 // [pos, head_dim/2] (cos, sin)
     int rope_cols, head_dim;             // columns [0, rope_cols) = q,k: rotated in (even, odd) pairs per head

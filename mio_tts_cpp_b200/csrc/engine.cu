@@ -387,6 +387,7 @@ void engine::gemm(const dbuf & a, const dev_linear & w, int M, int epilogue, voi
     g.map_b = w.map_b;
     g.map_out = omap(out, M, epilogue == EPI_SWIGLU16 ? w.N / 2 : w.N, ldo, epilogue == EPI_STORE32 ? 4 : 2);
     g.M = M; g.N = w.N; g.K = w.K; g.taps = w.taps;
+    g.tap_row0 = -(w.taps >> 1);   // k=3 "same" convolution over rows (taps == 1: plain GEMM)
     g.dtype = w.dtype; g.out_dtype = out_dtype; g.epilogue = epilogue;
     g.out = out; g.ldo = ldo; g.bias = bias; g.res = res; g.ldr = ldr;
     g.gate = gate; g.gate_ld = mdl->cond_total;

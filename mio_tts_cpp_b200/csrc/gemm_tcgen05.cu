@@ -220,7 +220,21 @@ __device__ __forceinline__ float silu_f(float x) { return __fdividef(x, 1.0f + _
 // Output boxes in shared memory use the TMA swizzle of their tensor map so that a quarter-warp's 16-byte accesses
 // hit 32 distinct banks: SWIZZLE_128B for 128-byte rows (fp32), SWIZZLE_64B for 64-byte rows (16-bit).
 
-// fp32 box: out = (acc + bias) * gate + residual, residual read from / result written to the same box slot.
+// ggml_gelu on the reference's CPU backend is a table over fp16 inputs: gelu(x) = fp16(gelu_tanh(fp16(x)))
+// (ggml-cpu/vec.h, GGML_GELU_FP16); the same two roundings are applied here so both sides agree to the fp16 ulp.
+__device__ __forceinline__ float act_apply(float x, int act) {
+    if (act == 1) {
+        const float h = __half2float(__float2half_rn(x));
+        const float u = 0.79788456080286535587989211986876f * h * (1.0f + 0.044715f * h * h);
+        const float t = 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * u));      // tanh(u)
+        const float y = __half2float(__float2half_rn(0.5f * h * (1.0f + t)));
+        return x <= -10.0f ? 0.0f : (x >= 10.0f ? x : y);
+    }
+    if (act == 2) return tanhf(x);
+    return x;
+}
+
+// fp32 box: out = act(acc + bias) * gate + residual, residual read from / result written to the same box slot.
 // BIAS/GATE/RES are compile-time so an absent term costs no issue slots; GUARD handles the last, partial N tile.
 template <bool BIAS, bool GATE, bool RES, bool GUARD>
 __device__ __forceinline__ void chunk_store32(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, int lane, int n,
@@ -238,6 +252,9 @@ __device__ __forceinline__ void chunk_store32(const gemm_args & a, const uint32_
         if (BIAS && in) {
             const float4 b = __ldg(bias4 + j);
             o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
+        }
+        if (a.act != 0) {   // warp-uniform
+            o.x = act_apply(o.x, a.act); o.y = act_apply(o.y, a.act); o.z = act_apply(o.z, a.act); o.w = act_apply(o.w, a.act);
         }
         if (GATE && in) {
             const float4 g = __ldg(gate4 + j);
@@ -300,6 +317,10 @@ __device__ __forceinline__ void chunk_store16(const gemm_args & a, const uint32_
                 const float4 b = __ldg(reinterpret_cast<const float4 *>(a.bias + n) + 2 * j + h);
                 x[4 * h] += b.x; x[4 * h + 1] += b.y; x[4 * h + 2] += b.z; x[4 * h + 3] += b.w;
             }
+        }
+        if (!ROPE && a.act != 0) {   // warp-uniform
+#pragma unroll
+            for (int e = 0; e < 8; ++e) x[e] = act_apply(x[e], a.act);
         }
         if constexpr (ROPE) {
 #pragma unroll
@@ -408,21 +429,22 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
                 const int m0 = (t / num_n_tiles) * TILE_M + cta_rank * BLOCK_M;
                 const int n0 = (t % num_n_tiles) * BN + cta_rank * C::B_ROWS;
                 for (int tap = 0; tap < a.taps; ++tap) {
-                    const int arow = m0 + tap - (a.taps >> 1);
+                    const int arow = m0 + a.tap_row0 + (tap >> a.tap_shift);
+                    const int acol = a.a_col0 + (tap & ((1 << a.tap_shift) - 1)) * a.K;
                     for (int kb = 0; kb < k_blocks; ++kb, ++kit) {
                         const int s = kit % C::STAGES;
                         mbar_wait(empty_bar(s), ((kit / C::STAGES) & 1) ^ 1);
                         const uint32_t sa = smem_base + s * C::STAGE_BYTES;
                         if constexpr (NCTA == 1) {
                             mbar_expect_tx(full_bar(s), C::STAGE_BYTES);
-                            tma_load_2d(sa, &a.map_a, full_bar(s), kb * BLOCK_K, arow);
+                            tma_load_2d(sa, &a.map_a, full_bar(s), acol + kb * BLOCK_K, arow);
 #pragma unroll
                             for (int bx = 0; bx < C::B_ROWS / B_BOX_ROWS; ++bx)
                                 tma_load_2d(sa + C::A_BYTES + bx * (B_BOX_ROWS * BLOCK_K * 2), &a.map_b, full_bar(s),
                                             tap * a.K + kb * BLOCK_K, n0 + bx * B_BOX_ROWS);
                         } else {
                             if (cta_rank == 0) mbar_expect_tx(full_bar(s), 2 * C::STAGE_BYTES);   // both CTAs' bytes
-                            tma_load_2d_pair(sa, &a.map_a, full_bar(s), kb * BLOCK_K, arow);
+                            tma_load_2d_pair(sa, &a.map_a, full_bar(s), acol + kb * BLOCK_K, arow);
 #pragma unroll
                             for (int bx = 0; bx < C::B_ROWS / B_BOX_ROWS; ++bx)
                                 tma_load_2d_pair(sa + C::A_BYTES + bx * (B_BOX_ROWS * BLOCK_K * 2), &a.map_b, full_bar(s),
@@ -509,7 +531,7 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
             const float4 * rope_row[EPI == EPI_ROPE16 ? 8 : 1];
             if constexpr (EPI == EPI_STORE32) {
                 if (a.gate) {
-                    const int utt = row0 + lane < a.M ? max(__ldg(a.row_utt + row0 + lane), 0) : 0;
+                    const int utt = (a.row_utt != nullptr && row0 + lane < a.M) ? max(__ldg(a.row_utt + row0 + lane), 0) : 0;
                     gate_row = a.gate + (size_t) utt * a.gate_ld;
                 }
             } else if constexpr (EPI == EPI_ROPE16) {

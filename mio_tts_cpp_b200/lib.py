@@ -91,6 +91,11 @@ def load_library():
         "mio_tts_b200_profile_resident": (C.c_bool, [vp, C.POINTER(Profile), cp, sz]),
         "mio_tts_b200_resident_samples": (u64, [vp]),
         "mio_tts_b200_istft_bench": (C.c_float, [vp, i32, i32, i32, i32, i32, u64, C.POINTER(C.c_double), cp, sz]),
+        "mio_tts_b200_reference_pcm_to_embedding_batch": (C.c_bool, [vp, C.POINTER(fp), szp, i32, sz, MioTtsParams, fpp, szp,
+                                                                     cp, sz]),
+        "mio_tts_b200_extract_ssl": (C.c_bool, [vp, fp, sz, i32, C.c_float, fpp, ip, ip, cp, sz]),
+        "mio_tts_b200_ssl_to_embedding": (C.c_bool, [vp, fp, i32, i32, fpp, szp, cp, sz]),
+        "mio_tts_b200_reference_bench": (C.c_float, [vp, fp, sz, i32, i32, i32, cp, sz]),
         "mio_tts_b200_launch_count": (u64, []),
         "mio_tts_b200_workspace_bytes": (u64, [vp]),
         "mio_tts_b200_weight_bytes": (u64, [vp]),
@@ -307,6 +312,67 @@ class MioTTS:
         if ms < 0:
             raise MioTtsError(self._err.value.decode())
         return float(ms), float(cs.value)
+
+    # ---- reference audio -> speaker embedding (WavLM + global encoder) ------------------------------------
+    def reference_to_embedding(self, wav_path, params=None):
+        p = params or self.default_params()
+        out, n = C.POINTER(C.c_float)(), C.c_size_t(0)
+        self._check(self.L.mio_tts_reference_to_embedding(self.ctx, wav_path.encode(), p, C.byref(out), C.byref(n), self._err,
+                                                          ERR_SIZE))
+        a = np.ctypeslib.as_array(out, shape=(n.value,)).copy()
+        self.L.mio_tts_embedding_free(out)
+        return a
+
+    def reference_pcm_to_embedding_batch(self, pcm_list, sample_rate, params=None):
+        p = params or self.default_params()
+        arrs = [_f32(x) for x in pcm_list]
+        b = len(arrs)
+        ptrs = (C.POINTER(C.c_float) * b)(*[_ptr(a, C.c_float) for a in arrs])
+        ns = (C.c_size_t * b)(*[a.size for a in arrs])
+        outs = (C.POINTER(C.c_float) * b)()
+        nout = (C.c_size_t * b)()
+        self._check(self.L.mio_tts_b200_reference_pcm_to_embedding_batch(self.ctx, ptrs, ns, sample_rate, b, p, outs, nout,
+                                                                         self._err, ERR_SIZE))
+        res = []
+        for i in range(b):
+            res.append(np.ctypeslib.as_array(outs[i], shape=(nout[i],)).copy())
+            self.L.mio_tts_embedding_free(outs[i])
+        return res
+
+    def extract_ssl(self, pcm, sample_rate, max_seconds=20.0):
+        x = _f32(pcm)
+        out = C.POINTER(C.c_float)()
+        nf, dim = C.c_int32(0), C.c_int32(0)
+        self._check(self.L.mio_tts_b200_extract_ssl(self.ctx, _ptr(x, C.c_float), x.size, sample_rate, max_seconds, C.byref(out),
+                                                    C.byref(nf), C.byref(dim), self._err, ERR_SIZE))
+        a = np.ctypeslib.as_array(out, shape=(nf.value, dim.value)).copy()
+        self.L.mio_tts_b200_free(out)
+        return a
+
+    def ssl_to_embedding(self, ssl):
+        x = _f32(ssl)
+        out, n = C.POINTER(C.c_float)(), C.c_size_t(0)
+        self._check(self.L.mio_tts_b200_ssl_to_embedding(self.ctx, _ptr(x, C.c_float), x.shape[0], x.shape[1], C.byref(out),
+                                                         C.byref(n), self._err, ERR_SIZE))
+        a = np.ctypeslib.as_array(out, shape=(n.value,)).copy()
+        self.L.mio_tts_embedding_free(out)
+        return a
+
+    def reference_bench(self, pcm, sample_rate, batch, iters):
+        x = _f32(pcm)
+        ms = self.L.mio_tts_b200_reference_bench(self.ctx, _ptr(x, C.c_float), x.size, sample_rate, batch, iters, self._err,
+                                                 ERR_SIZE)
+        if ms < 0:
+            raise MioTtsError(self._err.value.decode())
+        return float(ms)
+
+    def reserve_reference_workspace(self, max_seconds):
+        self._check(self.L.mio_tts_reserve_reference_workspace(self.ctx, max_seconds, self._err, ERR_SIZE))
+
+    def estimate_reference_workspace_bytes(self, max_seconds):
+        v = C.c_uint64(0)
+        self._check(self.L.mio_tts_estimate_reference_workspace_bytes(self.ctx, max_seconds, C.byref(v), self._err, ERR_SIZE))
+        return int(v.value)
 
     def launch_count(self):
         return int(self.L.mio_tts_b200_launch_count())

@@ -51,6 +51,46 @@ float * ref_istft(const float * spec, int n_frames, int n_fft, int hop, int n_th
     return out;
 }
 
+// --- reference-audio path --------------------------------------
+// wavlm_extractor::extract_ssl_features (src/wavlm-extractor.cpp:543): audio file -> ssl [n_frames][embed_dim]
+void * ref_wavlm_open(const char * gguf_path, char * err, size_t err_size) {
+    auto * w = new wavlm_extractor();
+    std::string e;
+    if (!w->load(gguf_path, e)) { set_err(err, err_size, e); delete w; return nullptr; }
+    std::string be;
+    w->set_backend_device("CPU", be);
+    return w;
+}
+void ref_wavlm_close(void * h) { delete (wavlm_extractor *) h; }
+
+bool ref_wavlm_extract(void * h, const char * audio_path, int source_sample_rate, float max_seconds, int n_threads,
+                       int flash, float ** ssl_out, int * n_frames_out, int * dim_out, char * err, size_t err_size) {
+    auto * w = (wavlm_extractor *) h;
+    std::vector<float> ssl; int nf = 0; std::string e;
+    if (!w->extract_ssl_features(audio_path, source_sample_rate, max_seconds, n_threads, (llama_flash_attn_type) flash,
+                                 ssl, nf, e)) {
+        set_err(err, err_size, e); return false;
+    }
+    if (!e.empty()) set_err(err, err_size, e);   // fallback notices are reported, the call still succeeds
+    float * out = (float *) std::malloc(std::max<size_t>(1, ssl.size()) * sizeof(float));
+    std::memcpy(out, ssl.data(), ssl.size() * sizeof(float));
+    *ssl_out = out; *n_frames_out = nf; *dim_out = nf > 0 ? (int) (ssl.size() / (size_t) nf) : 0;
+    return true;
+}
+
+// miocodec_decoder::encode_global_embedding_from_ssl (src/miocodec-decoder.cpp:824): ssl [n_frames][C] -> emb
+bool ref_decoder_encode_global(void * h, const float * ssl, int n_frames, int channels, int n_threads, float ** emb_out,
+                               int * n_emb_out, char * err, size_t err_size) {
+    auto * d = (miocodec_decoder *) h;
+    std::vector<float> s(ssl, ssl + (size_t) n_frames * channels), emb; std::string e;
+    if (!d->encode_global_embedding_from_ssl(s, n_frames, n_threads, emb, e)) { set_err(err, err_size, e); return false; }
+    if (!e.empty()) set_err(err, err_size, e);
+    float * out = (float *) std::malloc(std::max<size_t>(1, emb.size()) * sizeof(float));
+    std::memcpy(out, emb.data(), emb.size() * sizeof(float));
+    *emb_out = out; *n_emb_out = (int) emb.size();
+    return true;
+}
+
 void ref_free(void * p) { std::free(p); }
 
 int ref_hw_threads(void) { return (int) std::thread::hardware_concurrency(); }

@@ -60,6 +60,18 @@ class RefLib:
         L.ref_istft.restype = C.POINTER(C.c_float)
         L.ref_istft.argtypes = [C.POINTER(C.c_float), C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(sz)]
         L.ref_free.argtypes = [vp]
+        if hasattr(L, "ref_wavlm_open"):
+            fpp, ip = C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_int)
+            L.ref_wavlm_open.restype = vp
+            L.ref_wavlm_open.argtypes = [cp, cp, sz]
+            L.ref_wavlm_close.argtypes = [vp]
+            L.ref_wavlm_extract.restype = C.c_bool
+            L.ref_wavlm_extract.argtypes = [vp, cp, C.c_int, C.c_float, C.c_int, C.c_int, fpp, ip, ip, cp, sz]
+            L.ref_decoder_encode_global.restype = C.c_bool
+            L.ref_decoder_encode_global.argtypes = [vp, C.POINTER(C.c_float), C.c_int, C.c_int, C.c_int, fpp, ip, cp, sz]
+            L.mio_tts_reference_to_embedding.restype = C.c_bool
+            L.mio_tts_reference_to_embedding.argtypes = [vp, cp, MioTtsParams, fpp, C.POINTER(sz), cp, sz]
+            L.mio_tts_embedding_free.argtypes = [C.POINTER(C.c_float)]
         L.ref_hw_threads.restype = C.c_int
         L.mio_tts_init_from_file.restype = vp
         L.mio_tts_init_from_file.argtypes = [cp, cp, cp, sz]
@@ -101,6 +113,60 @@ class RefLib:
         self.lib.ref_free(out)
         return a
 
+    # --- wavlm_extractor::extract_ssl_features (src/wavlm-extractor.cpp:543) -> ssl [n_frames, embed_dim]
+    def open_wavlm(self, gguf_path):
+        err = C.create_string_buffer(512)
+        h = self.lib.ref_wavlm_open(gguf_path.encode(), err, 512)
+        if not h:
+            raise RuntimeError("ref_wavlm_open: " + err.value.decode())
+        return h
+
+    def close_wavlm(self, h):
+        self.lib.ref_wavlm_close(h)
+
+    def wavlm_extract(self, h, audio_path, source_sample_rate, max_seconds=20.0, n_threads=1, flash=0):
+        out = C.POINTER(C.c_float)()
+        nf, dim = C.c_int(0), C.c_int(0)
+        err = C.create_string_buffer(512)
+        ok = self.lib.ref_wavlm_extract(h, audio_path.encode(), source_sample_rate, max_seconds, n_threads, flash,
+                                        C.byref(out), C.byref(nf), C.byref(dim), err, 512)
+        if not ok:
+            raise RuntimeError("ref extract_ssl_features: " + err.value.decode())
+        if err.value:
+            raise RuntimeError("ref extract_ssl_features used a fallback: " + err.value.decode())
+        a = np.ctypeslib.as_array(out, shape=(nf.value, dim.value)).copy()
+        self.lib.ref_free(out)
+        return a
+
+    # --- miocodec_decoder::encode_global_embedding_from_ssl (src/miocodec-decoder.cpp:824)
+    def encode_global(self, h_decoder, ssl, n_threads=1):
+        ssl = np.ascontiguousarray(ssl, dtype=np.float32)
+        out = C.POINTER(C.c_float)()
+        n = C.c_int(0)
+        err = C.create_string_buffer(512)
+        ok = self.lib.ref_decoder_encode_global(h_decoder, ssl.ctypes.data_as(C.POINTER(C.c_float)), ssl.shape[0],
+                                                ssl.shape[1], n_threads, C.byref(out), C.byref(n), err, 512)
+        if not ok:
+            raise RuntimeError("ref encode_global_embedding_from_ssl: " + err.value.decode())
+        if err.value:
+            raise RuntimeError("ref encode_global_embedding_from_ssl fallback: " + err.value.decode())
+        a = np.ctypeslib.as_array(out, shape=(n.value,)).copy()
+        self.lib.ref_free(out)
+        return a
+
+    # --- mio_tts_reference_to_embedding (src/mio-tts-lib.cpp:1048)
+    def reference_to_embedding(self, ctx, audio_path, n_threads=0):
+        prm = MioTtsParams(n_threads, 20.0, 0, -1)
+        out = C.POINTER(C.c_float)()
+        n = C.c_size_t(0)
+        err = C.create_string_buffer(512)
+        ok = self.lib.mio_tts_reference_to_embedding(ctx, audio_path.encode(), prm, C.byref(out), C.byref(n), err, 512)
+        if not ok:
+            raise RuntimeError("mio_tts_reference_to_embedding: " + err.value.decode())
+        a = np.ctypeslib.as_array(out, shape=(n.value,)).copy()
+        self.lib.mio_tts_embedding_free(out)
+        return a
+
     # --- embd_to_audio (src/mio-tts-lib.cpp:625)
     def istft(self, spec, n_fft, hop, n_threads=1):
         spec = np.ascontiguousarray(spec, dtype=np.float32)
@@ -112,9 +178,9 @@ class RefLib:
         return a
 
     # --- mio_tts_synthesize (src/mio-tts-lib.cpp:1182)
-    def open_context(self, gguf_path):
+    def open_context(self, gguf_path, wavlm_path=None):
         err = C.create_string_buffer(512)
-        ctx = self.lib.mio_tts_init_from_file(gguf_path.encode(), None, err, 512)
+        ctx = self.lib.mio_tts_init_from_file(gguf_path.encode(), wavlm_path.encode() if wavlm_path else None, err, 512)
         if not ctx:
             raise RuntimeError("mio_tts_init_from_file: " + err.value.decode())
         if not self.lib.mio_tts_context_set_backend_device(ctx, b"CPU", err, 512):

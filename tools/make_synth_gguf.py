@@ -44,6 +44,26 @@ PRESETS = {
 }
 VOCAB = 12800  # codes 0..12799, /root/reference/src/mio-tts-lib.cpp:30-31
 
+# Global speaker-embedding encoder (optional tensors, /root/reference/src/miocodec-decoder.cpp:713-744; KVs :489-493;
+# graph :824-945).  "default" = the struct defaults (miocodec-decoder.h:44-48); "tiny" pairs with the tiny WavLM.
+GE_PRESETS = {
+    "default": dict(input_channels=768, output_channels=128, dim=384, intermediate_dim=1152, num_layers=4,
+                    embed_kernel=7, dw_kernel=7, attn_channels=128),
+    "tiny": dict(input_channels=128, output_channels=128, dim=64, intermediate_dim=128, num_layers=2,
+                 embed_kernel=7, dw_kernel=7, attn_channels=64),
+}
+
+# WavLM SSL extractor (/root/reference/src/wavlm-extractor.cpp:454-540 load, :664-865 graph;
+# scripts/convert_wavlm_base_plus_to_gguf.py:118-186 writer).  "base" = WavLM Base+ truncated to 2 layers.
+WAVLM_PRESETS = {
+    "base": dict(sample_rate=16000, n_layers=2, n_heads=12, head_dim=64, embed_dim=768, num_buckets=320,
+                 max_distance=800, conv_channels=512, ffn=3072, pos_kernel=128, pos_groups=16),
+    "tiny": dict(sample_rate=16000, n_layers=2, n_heads=2, head_dim=64, embed_dim=128, num_buckets=320,
+                 max_distance=800, conv_channels=64, ffn=256, pos_kernel=128, pos_groups=16),
+}
+WAVLM_CONV_K = [10, 3, 3, 3, 3, 2, 2]
+WAVLM_CONV_S = [5, 2, 2, 2, 2, 2, 2]
+
 
 def synth_tensors(cfg, seed=0):
     """Yield (name, ndarray) in a fixed order; numpy shapes are the reverse of ggml `ne`."""
@@ -128,7 +148,129 @@ def synth_tensors(cfg, seed=0):
     yield "istft_head.out.bias", hb
 
 
-def write_gguf(path, preset="default", seed=0):
+def synth_global_encoder_tensors(ge, seed=0):
+    """Global-encoder tensors in torch shapes (Conv1d [Cout, Cin/groups, K], Linear [out, in])."""
+    rng = np.random.default_rng(seed + 7001)
+    f32 = np.float32
+    cin, dim, ff, out, ac = ge["input_channels"], ge["dim"], ge["intermediate_dim"], ge["output_channels"], ge["attn_channels"]
+
+    def conv(o, i, k, gain=1.0):
+        return (rng.standard_normal((o, i, k)) * (gain / np.sqrt(i * k))).astype(f32)
+
+    def lin(o, i, gain=1.0):
+        return (rng.standard_normal((o, i)) * (gain / np.sqrt(i))).astype(f32)
+
+    def norm_w(c):
+        return (1.0 + 0.05 * rng.standard_normal(c)).astype(f32)
+
+    def small(c, sd=0.05):
+        return (sd * rng.standard_normal(c)).astype(f32)
+
+    g = "global_encoder."
+    yield g + "backbone.embed.weight", conv(dim, cin, ge["embed_kernel"])
+    yield g + "backbone.embed.bias", small(dim)
+    yield g + "backbone.norm.weight", norm_w(dim)
+    yield g + "backbone.norm.bias", small(dim)
+    for i in range(ge["num_layers"]):
+        b = g + f"backbone.blk.{i}."
+        yield b + "dwconv.weight", conv(dim, 1, ge["dw_kernel"])
+        yield b + "dwconv.bias", small(dim)
+        yield b + "norm.weight", norm_w(dim)
+        yield b + "norm.bias", small(dim)
+        yield b + "pw1.weight", lin(ff, dim)
+        yield b + "pw1.bias", small(ff)
+        yield b + "pw2.weight", lin(dim, ff)
+        yield b + "pw2.bias", small(dim)
+        yield b + "gamma", (0.5 + 0.1 * rng.standard_normal(dim)).astype(f32)
+    yield g + "backbone.final_norm.weight", norm_w(dim)
+    yield g + "backbone.final_norm.bias", small(dim)
+    yield g + "pool.attn0.weight", conv(ac, dim, 1)
+    yield g + "pool.attn0.bias", small(ac)
+    yield g + "pool.attn2.weight", conv(dim, ac, 1, 2.0)
+    yield g + "pool.attn2.bias", small(dim)
+    yield g + "pool.proj.weight", lin(out, 2 * dim)
+    yield g + "pool.proj.bias", small(out)
+    yield g + "pool.norm.weight", norm_w(out)
+    yield g + "pool.norm.bias", small(out)
+
+
+def synth_wavlm_tensors(cfg, seed=0):
+    rng = np.random.default_rng(seed + 9001)
+    f32 = np.float32
+    cc, ed, hd, nh, ff = cfg["conv_channels"], cfg["embed_dim"], cfg["head_dim"], cfg["n_heads"], cfg["ffn"]
+
+    def lin(o, i, gain=1.0):
+        return (rng.standard_normal((o, i)) * (gain / np.sqrt(i))).astype(f32)
+
+    def norm_w(c):
+        return (1.0 + 0.05 * rng.standard_normal(c)).astype(f32)
+
+    def small(c, sd=0.05):
+        return (sd * rng.standard_normal(c)).astype(f32)
+
+    yield "wavlm.feat.conv0.norm.weight", norm_w(cc)
+    yield "wavlm.feat.conv0.norm.bias", small(cc, 0.2)
+    yield "wavlm.feat.conv0.weight", (rng.standard_normal((cc, 1, WAVLM_CONV_K[0])) / np.sqrt(WAVLM_CONV_K[0])).astype(f32)
+    for i in range(1, 7):
+        k = WAVLM_CONV_K[i]
+        # gain > 1: GELU halves the variance layer after layer
+        yield f"wavlm.feat.conv{i}.weight", (rng.standard_normal((cc, cc, k)) * (1.6 / np.sqrt(cc * k))).astype(f32)
+    yield "wavlm.proj.norm.weight", norm_w(cc)
+    yield "wavlm.proj.norm.bias", small(cc)
+    yield "wavlm.proj.weight", lin(ed, cc)
+    yield "wavlm.proj.bias", small(ed)
+    yield "wavlm.pos_conv.weight", (rng.standard_normal((ed, ed // cfg["pos_groups"], cfg["pos_kernel"]))
+                                    / np.sqrt(ed // cfg["pos_groups"] * cfg["pos_kernel"])).astype(f32)
+    yield "wavlm.pos_conv.bias", small(ed)
+    yield "wavlm.transformer.norm.weight", norm_w(ed)
+    yield "wavlm.transformer.norm.bias", small(ed)
+    yield "wavlm.layer.0.attn.rel_embed.weight", (0.5 * rng.standard_normal((cfg["num_buckets"], nh))).astype(f32)
+    for i in range(cfg["n_layers"]):
+        p = f"wavlm.layer.{i}."
+        yield p + "attn.in_proj.weight", lin(3 * ed, ed)
+        yield p + "attn.in_proj.bias", small(3 * ed)
+        yield p + "attn.out_proj.weight", lin(ed, ed)
+        yield p + "attn.out_proj.bias", small(ed)
+        yield p + "attn.gru.weight", lin(8, hd)
+        yield p + "attn.gru.bias", small(8, 0.2)
+        yield p + "attn.gru_const", (1.0 + 0.1 * rng.standard_normal((1, nh, 1, 1))).astype(f32)
+        yield p + "norm1.weight", norm_w(ed)
+        yield p + "norm1.bias", small(ed)
+        yield p + "ffn.w1.weight", lin(ff, ed)
+        yield p + "ffn.w1.bias", small(ff)
+        yield p + "ffn.w2.weight", lin(ed, ff)
+        yield p + "ffn.w2.bias", small(ed)
+        yield p + "norm2.weight", norm_w(ed)
+        yield p + "norm2.bias", small(ed)
+
+
+def write_wavlm_gguf(path, preset="base", seed=0):
+    """WavLM SSL extractor GGUF with the names/KVs of scripts/convert_wavlm_base_plus_to_gguf.py:118-186."""
+    import gguf
+
+    cfg = WAVLM_PRESETS[preset]
+    w = gguf.GGUFWriter(path, "wavlm-ssl")
+    w.add_name(f"WavLM SSL extractor synthetic ({preset}, seed {seed})")
+    for k in ("sample_rate", "n_layers", "n_heads", "head_dim", "embed_dim", "num_buckets", "max_distance"):
+        w.add_uint32("wavlm." + k, int(cfg[k]))
+    w.add_float32("wavlm.layer_norm_eps", 1e-5)
+    for i, (k, st) in enumerate(zip(WAVLM_CONV_K, WAVLM_CONV_S)):
+        w.add_uint32(f"wavlm.feat.conv{i}.kernel", k)
+        w.add_uint32(f"wavlm.feat.conv{i}.stride", st)
+    n_params = 0
+    for name, arr in synth_wavlm_tensors(cfg, seed):
+        arr = np.ascontiguousarray(arr)
+        n_params += arr.size
+        w.add_tensor(name, arr)
+    w.write_header_to_file()
+    w.write_kv_data_to_file()
+    w.write_tensors_to_file()
+    w.close()
+    return n_params
+
+
+def write_gguf(path, preset="default", seed=0, global_encoder=None):
+    """global_encoder: None (decoder only, as the committed fixtures were made) or a GE_PRESETS key."""
     import gguf
 
     cfg = PRESETS[preset]
@@ -151,9 +293,15 @@ def write_gguf(path, preset="default", seed=0):
     if cfg["up_factors"]:
         w.add_tensor("miocodec.wave_upsampler.factors", np.asarray(cfg["up_factors"], dtype=np.int32))
         w.add_tensor("miocodec.wave_upsampler.kernel_sizes", np.asarray(cfg["up_kernels"], dtype=np.int32))
+    extra = []
+    if global_encoder is not None:
+        ge = GE_PRESETS[global_encoder]
+        for k in ("input_channels", "output_channels", "dim", "intermediate_dim", "num_layers"):
+            u32("miocodec.global_encoder." + k, int(ge[k]))
+        extra = list(synth_global_encoder_tensors(ge, seed))
     h = hashlib.sha256()
     n_params = 0
-    for name, arr in synth_tensors(cfg, seed):
+    for name, arr in list(synth_tensors(cfg, seed)) + extra:
         arr = np.ascontiguousarray(arr)
         h.update(name.encode())
         h.update(arr.tobytes())
