@@ -50,6 +50,33 @@ def synth_gguf(preset="default", tag=""):
     return path
 
 
+def reference_clip(seconds, sample_rate=24000, seed=3):
+    """Synthetic reference-audio clip (BASELINE config 4 stand-in: the reference's resources/ja_female.wav cannot travel):
+    a dozen amplitude-modulated partials plus noise, quantised to int16 steps so a 16-bit WAV holds it exactly."""
+    rng = np.random.default_rng(seed)
+    n = int(round(seconds * sample_rate))
+    t = np.arange(n) / sample_rate
+    x = np.zeros(n)
+    for _ in range(12):
+        f, a, ph = rng.uniform(80, 3000), rng.uniform(0.05, 0.3), rng.uniform(0, 6.28)
+        env = 0.5 * (1 + np.sin(2 * np.pi * rng.uniform(0.3, 3) * t + rng.uniform(0, 6.28)))
+        x += a * env * np.sin(2 * np.pi * f * t + ph)
+    x += 0.02 * rng.standard_normal(n)
+    x = x / np.abs(x).max() * 0.8
+    return (np.round(x * 32767) / 32768.0).astype(np.float32)
+
+
+def write_wav16(path, pcm, sample_rate):
+    """Mono PCM16 WAV of a clip whose samples are int16 steps / 32768 (reference_clip)."""
+    import wave
+
+    with wave.open(path, "wb") as w:
+        w.setnchannels(1)
+        w.setsampwidth(2)
+        w.setframerate(sample_rate)
+        w.writeframes(np.round(np.asarray(pcm, np.float64) * 32768.0).astype("<i2").tobytes())
+
+
 class ClockSampler:
     """Samples nvidia-smi clocks / throttle reasons of one GPU while a timed region runs."""
 

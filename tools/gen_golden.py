@@ -17,8 +17,16 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tools"))
 
-from make_synth_gguf import write_gguf  # noqa: E402
+from make_synth_gguf import write_gguf, write_wavlm_gguf  # noqa: E402
+from mio_tts_cpp_b200.benchutil import reference_clip, write_wav16  # noqa: E402
 from oracle.refbind import RefLib  # noqa: E402
+
+# reference-audio path: (fixture, wavlm preset, global-encoder preset, seconds, clip seed, ssl stride kept)
+REF_CASES = [
+    ("refemb_tiny", "tiny", "tiny", 2.0, 3, 1),
+    ("refemb_tiny_short", "tiny", "tiny", 0.31, 5, 1),
+    ("refemb_base", "base", "default", 3.0, 3, 4),
+]
 
 CASES = [  # (fixture, preset, T, codes seed)
     ("tiny_T50", "tiny", 50, 42),
@@ -67,5 +75,35 @@ def main():
         print("istft", n_fft, hop, audio.shape)
 
 
+def main_reference_path():
+    """wavlm_extractor::extract_ssl_features + encode_global_embedding_from_ssl + mio_tts_reference_to_embedding of the
+    compiled reference on seeded clips (written as 24 kHz PCM16 WAV, the codec rate, so miniaudio does not resample)."""
+    R = RefLib()
+    out_dir = os.path.join(ROOT, "tests", "golden")
+    for name, wl_preset, ge_preset, secs, seed, stride in REF_CASES:
+        dec, wl, wav = f"/tmp/mio_golden_dec_{ge_preset}.gguf", f"/tmp/mio_golden_wavlm_{wl_preset}.gguf", f"/tmp/mio_golden_{name}.wav"
+        write_gguf(dec, "tiny", 0, ge_preset)
+        write_wavlm_gguf(wl, wl_preset, 0)
+        write_wav16(wav, reference_clip(secs, 24000, seed), 24000)
+        h = R.open_wavlm(wl)
+        ssl = R.wavlm_extract(h, wav, 24000, 20.0, 4, 0)
+        R.close_wavlm(h)
+        d = R.open_decoder(dec)
+        emb_from_ssl = R.encode_global(d, ssl, 4)
+        R.close_decoder(d)
+        ctx = R.open_context(dec, wl)
+        emb = R.reference_to_embedding(ctx, wav, 4)
+        R.close_context(ctx)
+        assert np.array_equal(emb, emb_from_ssl)
+        np.savez_compressed(os.path.join(out_dir, name + ".npz"), wavlm_preset=wl_preset, ge_preset=ge_preset, seconds=secs,
+                            clip_seed=seed, ssl_stride=stride, n_frames=ssl.shape[0], ssl=ssl[::stride].astype(np.float32),
+                            ssl_row_norm=np.linalg.norm(ssl, axis=1).astype(np.float32), embedding=emb)
+        print(name, ssl.shape, float(ssl.std()), emb[:4])
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "reference":
+        main_reference_path()
+    else:
+        main()
+        main_reference_path()
