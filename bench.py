@@ -150,18 +150,20 @@ def run_b200(args, rank, world, local_rank):
     # mio_tts_b200_synthesize_batch on a full 64 x 400 batch per step, so one slot's D2H overlaps another's kernels.
     import threading
 
-    def e2e_run(n_slots, steps):
+    def e2e_run(n_slots, steps, wav16=False):
         slots = [m] + [m.clone() for _ in range(n_slots - 1)]
         work = [U.config2_workload(rank * 16 + i, BATCH, N_CODES) for i in range(n_slots)]
+        call = (lambda s, w: s.synthesize_wav16_batch(w, embs, copy=False)) if wav16 else \
+               (lambda s, w: s.synthesize_batch(w, embs, copy=False))
         for s, w in zip(slots, work):
             for _ in range(2):
-                s.synthesize_batch(w, embs, copy=False)
+                call(s, w)
         gate = threading.Barrier(n_slots + 1)
 
         def loop(s, w):
             gate.wait()
             for _ in range(steps):
-                s.synthesize_batch(w, embs, copy=False)
+                call(s, w)
             gate.wait()
 
         th = [threading.Thread(target=loop, args=(s, w)) for s, w in zip(slots, work)]
@@ -182,6 +184,7 @@ def run_b200(args, rank, world, local_rank):
     e2e_single_s = max_over_ranks(e2e_run(1, args.steps))
     e2e_s = max_over_ranks(e2e_run(args.e2e_slots, args.steps)) if args.e2e_slots > 1 else e2e_single_s
     e2e = total_audio / e2e_s
+    e2e_wav_s = max_over_ranks(e2e_run(args.e2e_slots, args.steps, wav16=True))
     h2d = m.last_h2d_bytes()
     d2h = int(m.resident_samples() * 4)
 
@@ -195,9 +198,12 @@ def run_b200(args, rank, world, local_rank):
             "e2e": {"value": e2e, "unit": "audio-seconds/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": d2h,
                     "ms_per_step": 1e3 * e2e_s, "slots": args.e2e_slots,
                     "single_slot_value": total_audio / e2e_single_s, "single_slot_ms_per_step": 1e3 * e2e_single_s,
+                    "wav16_value": total_audio / e2e_wav_s, "wav16_d2h_bytes_per_step": d2h // 2 + 44 * BATCH,
                     "note": "a step = one mio_tts_b200_synthesize_batch call (64 x 400 codes from host memory to pinned "
                             "host waveforms); `slots` host threads with one context clone each, as the reference "
-                            "server runs its slots; single_slot_* = one caller, nothing overlapped"},
+                            "server runs its slots; single_slot_* = one caller, nothing overlapped; wav16_* = the same "
+                            "slots asking for audio/wav bodies (mio_tts_b200_synthesize_wav16_batch: int16 conversion on "
+                            "the GPU, half the D2H bytes), which is what the reference server sends"},
             "gpu_launches": int(launches), "clocks": cs.summary()}
 
     if rank == 0:
@@ -222,6 +228,8 @@ def run_b200(args, rank, world, local_rank):
                             / peaks["bf16_tflops_sustained"] if world == 1 else None}
         line["stages_ms"] = {k: p[k] for k in ("prenet_ms", "upsample_prior_ms", "decoder_ms", "post_head_ms", "istft_ms",
                                                "total_ms", "attn_ms")}
+        if world == 1 and not args.skip_aux:
+            line["aux"] = aux_configs(m, peaks)
         if world == 1 and not args.skip_cpu:
             # ---- CPU baseline: the unmodified reference on this box's host cores, bounded sample ----
             n_cpu = BATCH   # the whole config-2 batch, one utterance after another (~10-30 s of host work)
@@ -236,6 +244,45 @@ def run_b200(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def aux_configs(m, peaks):
+    """Side measurements next to the headline (not bench lines of their own): BASELINE config 3 (iSTFT alone over 1 M
+    frames, HBM roofline) and config 4 (WavLM 2-layer + global encoder, 32 clips x 10 s, inputs resident)."""
+    from mio_tts_cpp_b200 import MioTTS
+
+    out = {}
+    n_utt, frames = 1000, 1000
+    ms, _ = m.istft_bench(n_utt, frames, 1920, 480, 5)
+    gbs = n_utt * frames * U.ISTFT_BYTES_PER_FRAME / (ms * 1e-3) / 1e9
+    out["config3_istft"] = {"frames": n_utt * frames, "n_fft": 1920, "hop": 480, "ms": ms, "frames_per_s": n_utt * frames / (ms * 1e-3),
+                            "roofline": {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                                         "frac": gbs / peaks["hbm_gbs"]}}
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    from make_synth_gguf import write_gguf, write_wavlm_gguf
+
+    dec, wl = "/tmp/mio_bench_tiny_ge.gguf", "/tmp/mio_bench_wavlm_base.gguf"
+    if not os.path.exists(dec):
+        write_gguf(dec + ".tmp", "tiny", 0, "default")
+        os.replace(dec + ".tmp", dec)
+    if not os.path.exists(wl):
+        write_wavlm_gguf(wl + ".tmp", "base", 0)
+        os.replace(wl + ".tmp", wl)
+    r = MioTTS(dec, wl)
+    clip = U.reference_clip(10.0, 24000, 3)
+    ms = r.reference_bench(clip, 24000, 32, 10)
+    t0 = time.perf_counter()
+    n_e2e = 5
+    for _ in range(n_e2e):
+        r.reference_pcm_to_embedding_batch([clip] * 32, 24000)
+    e2e_ms = 1e3 * (time.perf_counter() - t0) / n_e2e
+    r.free()
+    out["config4_reference_embedding"] = {"clips": 32, "seconds_per_clip": 10.0, "ms_per_batch": ms, "clips_per_s": 32 / (ms * 1e-3),
+                                          "e2e_ms_per_batch": e2e_ms, "e2e_clips_per_s": 32 / (e2e_ms * 1e-3),
+                                          "h2d_bytes_per_batch": 32 * clip.size * 4,
+                                          "note": "WavLM base-size synthetic weights (2 layers, 768/12/3072) + default global "
+                                                  "encoder; e2e = host PCM in, host embeddings out"}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -243,6 +290,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--skip-cpu", action="store_true", help="omit the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--skip-aux", action="store_true", help="omit the config-3 / config-4 side measurements")
     ap.add_argument("--e2e-slots", type=int, default=2, help="host threads (context clones) of the end-to-end leg")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

@@ -149,6 +149,38 @@ MIO_B200_API bool mio_tts_b200_synthesize_batch(struct mio_tts_context * ctx, co
                                                 float ** audio_out, size_t * n_audio_out, int32_t * sample_rate_out,
                                                 char * err, size_t err_size);
 
+/* The same batch, returned as ready-to-send `audio/wav` bodies: wav_out[i] = 44-byte RIFF/WAVE header + 16-bit mono PCM,
+ * wav_bytes_out[i] = 44 + 2 * samples.  Replaces the server's float -> int16 loop and header writer
+ * (/root/reference/src/tts-mio-server.cpp:3965-3973, build_wav_header :2013-2034; same rounding as save_wav16,
+ * src/mio-tts-lib.cpp:781-785: clamp to [-1, 1], lrintf(x * 32767)), after the peak normaliser (lib.cpp:1299-1310).
+ * The conversion runs on the GPU, so the device -> host copy is half the bytes.  Free each with mio_tts_b200_wav_free.
+ * sample_rate_out may be NULL. */
+MIO_B200_API bool mio_tts_b200_synthesize_wav16_batch(struct mio_tts_context * ctx, const int32_t * const * codes,
+                                                      const size_t * n_codes, const float * const * embedding,
+                                                      size_t n_embedding, size_t batch, struct mio_tts_params params,
+                                                      uint8_t ** wav_out, size_t * wav_bytes_out, int32_t * sample_rate_out,
+                                                      char * err, size_t err_size);
+MIO_B200_API void mio_tts_b200_wav_free(uint8_t * wav);
+
+/* Micro-batcher for server slots.  The reference serialises the slots of one device on the owner's
+ * runtime mutex (src/tts-mio-server.cpp:2659-2670, 2724-2736; src/mio-tts-lib.cpp:1258-1262).  After this call,
+ * mio_tts_synthesize (and batch-of-one calls of the two batch entry points) on `ctx` AND ON EVERY CLONE MADE AFTERWARDS
+ * are queued and decoded together: up to max_batch utterances per launch, waiting at most max_wait_us for the callers
+ * released by the previous batch to come back; `workers` engines (default 2) overlap one batch's device -> host copy with
+ * the next batch's kernels.  Results are bit-identical to un-batched calls; a request that fails (e.g. an out-of-range
+ * code) fails alone with its usual message.  max_batch <= 0 turns batching off for this context.
+ * MIO_TTS_B200_BATCHING="max_batch[,max_wait_us[,workers]]" enables it at mio_tts_init_from_file without code changes. */
+MIO_B200_API bool mio_tts_b200_context_enable_batching(struct mio_tts_context * ctx, int32_t max_batch, int32_t max_wait_us,
+                                                       int32_t workers, char * err, size_t err_size);
+/* counters since the batcher was created; false when batching is off.  Any output pointer may be NULL. */
+MIO_B200_API bool mio_tts_b200_batching_stats(struct mio_tts_context * ctx, uint64_t * requests, uint64_t * batches,
+                                              uint64_t * largest, uint64_t * retried_single);
+
+/* Test hook: the WAV16 conversion kernel alone (peak rule lib.cpp:1299-1310 + clamp/round :781-785) over host waveforms;
+ * pcm_out[i] = malloc'd n_audio[i] samples, release with mio_tts_b200_free. */
+MIO_B200_API bool mio_tts_b200_audio_to_pcm16(struct mio_tts_context * ctx, const float * const * audio, const size_t * n_audio,
+                                              size_t batch, int16_t ** pcm_out, char * err, size_t err_size);
+
 /* Stage hooks for parity tests.  decode_spec mirrors miocodec_decoder::decode_tokens
  * (/root/reference/src/miocodec-decoder.cpp:1079): spec_out = malloc'd [n_frames][n_bins]. */
 MIO_B200_API bool mio_tts_b200_decode_spec(struct mio_tts_context * ctx, const int32_t * codes, size_t n_codes,

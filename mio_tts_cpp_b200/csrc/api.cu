@@ -3,6 +3,7 @@
 // (cited below as lib.cpp:LINE); the decode itself runs on the GPU through mio::engine, with no CPU fallback.
 #include "../../include/mio_tts_b200.h"
 
+#include "batcher.h"
 #include "engine.h"
 #include "gguf_io.h"
 #include "refenc.h"
@@ -27,6 +28,7 @@ struct mio_tts_context {
     std::unique_ptr<engine> eng;
     std::shared_ptr<refmodel> ref;      // WavLM + global-encoder weights (reference-audio path), shared by clones
     std::unique_ptr<refenc> renc;       // per-context stream + workspace of that path
+    std::shared_ptr<batcher> bat;       // micro-batcher shared with the clones (null: calls decode on this context's engine)
     std::string vocoder_path, wavlm_path;
 };
 
@@ -41,6 +43,16 @@ constexpr int32_t k_code_min = 0, k_code_max = 12799;                 // lib.cpp
 
 void set_err(char * err, size_t err_size, const std::string & msg) {   // lib.cpp:65-69
     if (err != nullptr && err_size > 0) std::snprintf(err, err_size, "%s", msg.c_str());
+}
+
+// MIO_TTS_B200_BATCHING="max_batch[,max_wait_us[,workers]]": contexts created by mio_tts_init_from_file start with the
+// micro-batcher on, so an unmodified server gets coalesced slots (batcher.h)
+bool env_batching(int out[3]) {
+    const char * e = std::getenv("MIO_TTS_B200_BATCHING");
+    if (e == nullptr || e[0] == '\0' || (e[0] == '0' && e[1] == '\0')) return false;
+    out[0] = 64; out[1] = 300; out[2] = 2;
+    std::sscanf(e, "%d,%d,%d", &out[0], &out[1], &out[2]);
+    return out[0] > 0;
 }
 
 // "CUDA3" / "cuda:3" / "3" -> 3; "" -> -1 (keep); anything else -> -2
@@ -260,6 +272,8 @@ struct mio_tts_context * mio_tts_init_from_file(const char * model_vocoder, cons
         ctx->renc.reset(new refenc(r));
         ctx->vocoder_path = model_vocoder;
         ctx->wavlm_path = wavlm;
+        int bp[3];
+        if (env_batching(bp)) ctx->bat = std::make_shared<batcher>(m, bp[0], bp[1], bp[2]);
     });
     if (!ok) { delete ctx; return nullptr; }
     return ctx;
@@ -276,6 +290,7 @@ struct mio_tts_context * mio_tts_context_clone(const struct mio_tts_context * ct
         out->mdl = ctx->mdl;
         out->eng.reset(new engine(ctx->mdl));
         out->ref = ctx->ref;
+        out->bat = ctx->bat;     // the slots of one device feed one batcher
         if (ctx->ref) out->renc.reset(new refenc(ctx->ref));
         out->vocoder_path = ctx->vocoder_path;
         out->wavlm_path = ctx->wavlm_path;
@@ -328,6 +343,7 @@ bool mio_tts_context_set_backend_device(struct mio_tts_context * ctx, const char
         ctx->ref = r;
         ctx->eng.reset(new engine(m));
         ctx->renc.reset(new refenc(r));
+        if (ctx->bat) ctx->bat = std::make_shared<batcher>(m, ctx->bat->max_batch, ctx->bat->max_wait_us, ctx->bat->workers);
     });
 }
 
@@ -606,38 +622,77 @@ bool mio_tts_embedding_save_gguf(const char * path, const float * embedding, siz
 
 void mio_tts_embedding_free(float * embedding) { std::free(embedding); }
 
-bool mio_tts_b200_synthesize_batch(struct mio_tts_context * ctx, const int32_t * const * codes, const size_t * n_codes,
-                                   const float * const * embedding, size_t n_embedding, size_t batch,
-                                   struct mio_tts_params, float ** audio_out, size_t * n_audio_out,
-                                   int32_t * sample_rate_out, char * err, size_t err_size) {
+// shared body of the batch entry points: fp32 waveforms (wav16 = false) or RIFF/WAVE 16-bit buffers (wav16 = true)
+static bool synthesize_batch_any(struct mio_tts_context * ctx, const int32_t * const * codes, const size_t * n_codes,
+                                 const float * const * embedding, size_t n_embedding, size_t batch, bool wav16, void ** out,
+                                 size_t * n_out, int32_t * sample_rate_out, char * err, size_t err_size) {
     if (ctx == nullptr || !ctx->mdl) { set_err(err, err_size, "context is null"); return false; }
     if (codes == nullptr || n_codes == nullptr || batch == 0) { set_err(err, err_size, "codes are empty"); return false; }
     for (size_t u = 0; u < batch; ++u)
         if (codes[u] == nullptr || n_codes[u] == 0) { set_err(err, err_size, "codes are empty"); return false; }
-    if (audio_out == nullptr || n_audio_out == nullptr || sample_rate_out == nullptr) {
+    if (out == nullptr || n_out == nullptr || (!wav16 && sample_rate_out == nullptr)) {   // the WAV header carries the rate
         set_err(err, err_size, "output pointers are null");
         return false;
     }
-    std::vector<float *> bufs(batch, nullptr);
-    const bool ok = guarded(err, err_size, [&] {
-        std::lock_guard<std::mutex> lk(ctx->eng->mtx);
-        engine & E = *ctx->eng;
-        E.prepare(codes, n_codes, embedding, n_embedding, batch);
-        E.run(true);
-        for (size_t u = 0; u < batch; ++u) {
-            bufs[u] = result_alloc(E.audio_len(u));
-            if (bufs[u] == nullptr) throw std::runtime_error("failed to allocate output audio");
-            E.fetch_audio(u, bufs[u]);
-        }
-        E.sync();
-        for (size_t u = 0; u < batch; ++u) { audio_out[u] = bufs[u]; n_audio_out[u] = E.audio_len(u); }
-        *sample_rate_out = ctx->mdl->hp.sample_rate;
-    });
-    if (!ok) {
-        try { ctx->eng->sync(); } catch (...) {}
-        for (float * p : bufs) if (p && !result_free(p)) std::free(p);
+    const bool has_emb = embedding != nullptr && n_embedding > 0;
+    std::vector<decode_request> reqs(batch);
+    std::vector<decode_request *> rp(batch);
+    for (size_t u = 0; u < batch; ++u) {
+        reqs[u].codes = codes[u]; reqs[u].n_codes = n_codes[u];
+        reqs[u].emb = has_emb ? embedding[u] : nullptr; reqs[u].n_emb = has_emb ? n_embedding : 0;
+        reqs[u].wav16 = wav16;
+        rp[u] = &reqs[u];
     }
-    return ok;
+    if (batch == 1 && ctx->bat) {
+        ctx->bat->submit(reqs[0]);             // coalesced with whatever the other slots have queued
+        if (!reqs[0].ok) { set_err(err, err_size, reqs[0].err); return false; }
+    } else if (!guarded(err, err_size, [&] { decode_batch(*ctx->eng, rp.data(), batch); })) {
+        return false;
+    }
+    for (size_t u = 0; u < batch; ++u) { out[u] = reqs[u].out; n_out[u] = wav16 ? 44 + 2 * reqs[u].n_samples : reqs[u].n_samples; }
+    if (sample_rate_out) *sample_rate_out = ctx->mdl->hp.sample_rate;
+    return true;
+}
+
+bool mio_tts_b200_synthesize_batch(struct mio_tts_context * ctx, const int32_t * const * codes, const size_t * n_codes,
+                                   const float * const * embedding, size_t n_embedding, size_t batch,
+                                   struct mio_tts_params, float ** audio_out, size_t * n_audio_out,
+                                   int32_t * sample_rate_out, char * err, size_t err_size) {
+    return synthesize_batch_any(ctx, codes, n_codes, embedding, n_embedding, batch, false, (void **) audio_out, n_audio_out,
+                                sample_rate_out, err, err_size);
+}
+
+bool mio_tts_b200_synthesize_wav16_batch(struct mio_tts_context * ctx, const int32_t * const * codes, const size_t * n_codes,
+                                         const float * const * embedding, size_t n_embedding, size_t batch,
+                                         struct mio_tts_params, uint8_t ** wav_out, size_t * wav_bytes_out,
+                                         int32_t * sample_rate_out, char * err, size_t err_size) {
+    return synthesize_batch_any(ctx, codes, n_codes, embedding, n_embedding, batch, true, (void **) wav_out, wav_bytes_out,
+                                sample_rate_out, err, err_size);
+}
+
+void mio_tts_b200_wav_free(uint8_t * wav) {
+    if (wav == nullptr) return;
+    if (!result_free(wav)) std::free(wav);
+}
+
+bool mio_tts_b200_context_enable_batching(struct mio_tts_context * ctx, int32_t max_batch, int32_t max_wait_us, int32_t workers,
+                                          char * err, size_t err_size) {
+    if (ctx == nullptr || !ctx->mdl) { set_err(err, err_size, "context is null"); return false; }
+    if (max_batch <= 0) { ctx->bat.reset(); return true; }
+    return guarded(err, err_size, [&] {
+        ctx->bat = std::make_shared<batcher>(ctx->mdl, max_batch, max_wait_us, workers <= 0 ? 2 : workers);
+    });
+}
+
+bool mio_tts_b200_batching_stats(struct mio_tts_context * ctx, uint64_t * requests, uint64_t * batches, uint64_t * largest,
+                                 uint64_t * retried_single) {
+    if (ctx == nullptr || !ctx->bat) return false;
+    const batcher_stats st = ctx->bat->stats();
+    if (requests) *requests = st.requests;
+    if (batches) *batches = st.batches;
+    if (largest) *largest = st.largest;
+    if (retried_single) *retried_single = st.retried_single;
+    return true;
 }
 
 bool mio_tts_synthesize(struct mio_tts_context * ctx, const int32_t * codes, size_t n_codes, const float * embedding,
@@ -918,6 +973,25 @@ uint64_t mio_tts_b200_resident_samples(struct mio_tts_context * ctx) {
     uint64_t n = 0;
     for (size_t u = 0; u < ctx->eng->batch(); ++u) n += ctx->eng->audio_len(u);
     return n;
+}
+
+bool mio_tts_b200_audio_to_pcm16(struct mio_tts_context * ctx, const float * const * audio, const size_t * n_audio, size_t batch,
+                                 int16_t ** pcm_out, char * err, size_t err_size) {
+    if (ctx == nullptr || !ctx->mdl) { set_err(err, err_size, "context is null"); return false; }
+    if (audio == nullptr || n_audio == nullptr || pcm_out == nullptr || batch == 0) { set_err(err, err_size, "audio is empty"); return false; }
+    std::vector<int16_t *> bufs(batch, nullptr);
+    const bool ok = guarded(err, err_size, [&] {
+        for (size_t u = 0; u < batch; ++u) {
+            if (audio[u] == nullptr || n_audio[u] == 0) throw std::runtime_error("audio is empty");
+            bufs[u] = (int16_t *) std::malloc(n_audio[u] * 2);
+            if (bufs[u] == nullptr) throw std::runtime_error("failed to allocate output audio");
+        }
+        std::lock_guard<std::mutex> lk(ctx->eng->mtx);
+        ctx->eng->pcm16_host(audio, n_audio, batch, bufs.data());
+    });
+    if (!ok) { for (int16_t * p : bufs) std::free(p); return false; }
+    for (size_t u = 0; u < batch; ++u) pcm_out[u] = bufs[u];
+    return true;
 }
 
 float mio_tts_b200_istft_bench(struct mio_tts_context * ctx, int32_t n_utt, int32_t frames_per_utt, int32_t n_fft,

@@ -165,5 +165,7 @@ void launch_istft(const istft_plan & p, const float * spec, int pitch, const int
                   cudaStream_t st);
 void launch_peak_normalize(float * audio, const long long * audio_off, const long long * audio_len,
                            const unsigned int * peak_bits, int n_utt, long long max_len, cudaStream_t st);
+void launch_pcm16(const float * audio, const long long * audio_off, const long long * audio_len, const unsigned int * peak_bits,
+                  int16_t * pcm, int n_utt, long long max_len, cudaStream_t st);
 
 } // namespace mio

@@ -83,7 +83,7 @@ engine::~engine() {
     cudaSetDevice(mdl->device);
     if (st_) cudaStreamSynchronize(st_);
     for (dbuf * b : {&xt_, &fx_, &fy_, &ft_, &act16_, &qkv16_, &att16_, &ff16_, &cond_, &gn_stats_, &gn_mr_, &spec_buf_,
-                     &audio_, &peak_, &d_blob_})
+                     &audio_, &peak_, &pcm_, &d_blob_})
         if (b->p) cudaFree(b->p);
     if (h_blob_) cudaFreeHost(h_blob_);
     if (rope_p_) cudaFree(rope_p_);
@@ -111,7 +111,7 @@ void engine::ensure(dbuf & b, size_t bytes) {
 size_t engine::workspace_bytes() const {
     size_t s = 0;
     for (const dbuf * b : {&xt_, &fx_, &fy_, &ft_, &act16_, &qkv16_, &att16_, &ff16_, &cond_, &gn_stats_, &gn_mr_,
-                           &spec_buf_, &audio_, &peak_, &d_blob_})
+                           &spec_buf_, &audio_, &peak_, &pcm_, &d_blob_})
         s += b->cap;
     return s;
 }
@@ -555,8 +555,14 @@ void engine::run(bool with_istft, stage_times * prof, int stop_stage) {
                      (float *) audio_.p, (unsigned int *) peak_.p, n_utt_, spec_->max_len, st_);
         long long max_len = 0;
         for (auto l : audio_len_) max_len = std::max(max_len, l);
-        launch_peak_normalize((float *) audio_.p, d_audio_off_, d_audio_len_, (const unsigned int *) peak_.p, n_utt_,
-                              max_len, st_);
+        if (out_pcm16) {   // WAV16 samples for the server's response instead of the normalised fp32 waveform
+            ensure(pcm_, (size_t) audio_total_ * 2 + 256);
+            launch_pcm16((const float *) audio_.p, d_audio_off_, d_audio_len_, (const unsigned int *) peak_.p,
+                         (int16_t *) pcm_.p, n_utt_, max_len, st_);
+        } else {
+            launch_peak_normalize((float *) audio_.p, d_audio_off_, d_audio_len_, (const unsigned int *) peak_.p, n_utt_,
+                                  max_len, st_);
+        }
     }
     mark(5);
 
@@ -589,6 +595,45 @@ void engine::run(bool with_istft, stage_times * prof, int stop_stage) {
 void engine::fetch_audio(size_t u, float * dst) {
     MIO_CUDA(cudaMemcpyAsync(dst, (const float *) audio_.p + audio_off_[u], (size_t) audio_len_[u] * sizeof(float),
                              cudaMemcpyDeviceToHost, st_));
+}
+
+void engine::fetch_pcm16(size_t u, int16_t * dst) {
+    if (pcm_.p == nullptr) throw std::runtime_error("no WAV16 samples: the last run produced fp32 audio");
+    MIO_CUDA(cudaMemcpyAsync(dst, (const int16_t *) pcm_.p + audio_off_[u], (size_t) audio_len_[u] * sizeof(int16_t),
+                             cudaMemcpyDeviceToHost, st_));
+}
+
+// Test hook for pcm16_kernel alone: host waveforms in (un-normalised), int16 out; the peak that the iSTFT kernel
+// would have left in peak_ is taken on the host here.
+void engine::pcm16_host(const float * const * audio, const size_t * n, size_t batch, int16_t * const * out) {
+    MIO_CUDA(cudaSetDevice(mdl->device));
+    std::vector<long long> off(batch), len(batch);
+    std::vector<unsigned int> peak(batch);
+    long long total = 0, max_len = 0;
+    for (size_t u = 0; u < batch; ++u) {
+        off[u] = total; len[u] = (long long) n[u];
+        total += (long long) round_up(n[u], 64);
+        max_len = std::max(max_len, len[u]);
+        float pk = 0.0f;
+        for (size_t i = 0; i < n[u]; ++i) { const float a = std::fabs(audio[u][i]); if (std::isfinite(a)) pk = std::max(pk, a); }
+        std::memcpy(&peak[u], &pk, 4);
+    }
+    ensure(audio_, (size_t) total * 4 + 256);
+    ensure(pcm_, (size_t) total * 2 + 256);
+    ensure(peak_, batch * 4 + 256);
+    blob_.clear();
+    const size_t o_off = blob_add(off.data(), batch * 8), o_len = blob_add(len.data(), batch * 8);
+    ensure(d_blob_, blob_.size() + 256);
+    MIO_CUDA(cudaMemcpyAsync(d_blob_.p, blob_.data(), blob_.size(), cudaMemcpyHostToDevice, st_));
+    MIO_CUDA(cudaMemcpyAsync(peak_.p, peak.data(), batch * 4, cudaMemcpyHostToDevice, st_));
+    for (size_t u = 0; u < batch; ++u)
+        MIO_CUDA(cudaMemcpyAsync((float *) audio_.p + off[u], audio[u], n[u] * 4, cudaMemcpyHostToDevice, st_));
+    const uint8_t * b = (const uint8_t *) d_blob_.p;
+    launch_pcm16((const float *) audio_.p, (const long long *) (b + o_off), (const long long *) (b + o_len),
+                 (const unsigned int *) peak_.p, (int16_t *) pcm_.p, (int) batch, max_len, st_);
+    for (size_t u = 0; u < batch; ++u)
+        MIO_CUDA(cudaMemcpyAsync(out[u], (const int16_t *) pcm_.p + off[u], n[u] * 2, cudaMemcpyDeviceToHost, st_));
+    MIO_CUDA(cudaStreamSynchronize(st_));
 }
 
 void engine::fetch_debug(std::vector<float> & out, int & rows, int & cols) {

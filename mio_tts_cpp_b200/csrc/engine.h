@@ -58,18 +58,21 @@ public:
     int spec_frames(size_t u) const { return spec_->len[u]; }
     int spec_bins() const { return mdl->hp.n_fft + 2; }
     void fetch_audio(size_t u, float * dst);   // async D2H on the engine's stream (call sync() afterwards)
+    void fetch_pcm16(size_t u, int16_t * dst); // after a run with out_pcm16 (async D2H)
     void fetch_spec(size_t u, float * dst);    // dense [frames, n_bins]
     size_t h2d_bytes() const { return h2d_bytes_; }
 
     // stand-alone stages for the parity tests / microbench (host in, host out)
     void gather(const int32_t * codes, size_t n, float * out);
     void istft_host(const float * spec, int n_frames, int n_fft, int hop, std::vector<float> & audio);
+    void pcm16_host(const float * const * audio, const size_t * n, size_t batch, int16_t * const * out);
     // resident iSTFT microbench: `n_utt` utterances x `frames` frames of synthetic spectra already in HBM
     float istft_bench(int n_utt, int frames, int n_fft, int hop, int iters, unsigned long long seed, double * checksum);
 
     size_t workspace_bytes() const;
     void reserve(int n_codes, int batch);
     bool force_generic_attention = false;
+    bool out_pcm16 = false;     // run(): emit clamp/round int16 samples (pcm16_kernel) instead of normalising the fp32 waveform
     cudaStream_t stream() const { return st_; }
     std::mutex mtx;
 
@@ -101,7 +104,7 @@ private:
     const long long * d_audio_off_ = nullptr, * d_audio_len_ = nullptr;
 
     // workspace
-    dbuf xt_, fx_, fy_, ft_, act16_, qkv16_, att16_, ff16_, cond_, gn_stats_, gn_mr_, spec_buf_, audio_, peak_;
+    dbuf xt_, fx_, fy_, ft_, act16_, qkv16_, att16_, ff16_, cond_, gn_stats_, gn_mr_, spec_buf_, audio_, peak_, pcm_;
     int spec_pitch_ = 0;
     const void * dbg_ptr_ = nullptr; int dbg_cols_ = 0, dbg_is16_ = 0, dbg_dtype_ = 0; const seq_layout * dbg_lay_ = nullptr;
     float2 * rope_p_ = nullptr, * rope_d_ = nullptr; int rope_p_pos_ = 0, rope_d_pos_ = 0;

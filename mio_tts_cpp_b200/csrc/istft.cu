@@ -277,6 +277,35 @@ __global__ void peak_normalize_kernel(float * __restrict__ audio, const long lon
         p[i] *= gain;
 }
 
+// Peak normaliser + WAV16 sample emission in one pass (server response path: /root/reference/src/tts-mio-server.cpp:3965-3973,
+// same rule as save_wav16, src/mio-tts-lib.cpp:781-785): y = clamp(x * gain, -1, 1); pcm = (int16) lrintf(y * 32767).
+// The fp32 waveform is left untouched (un-normalised); each product is rounded separately like the reference's two loops.
+__global__ void pcm16_kernel(const float * __restrict__ audio, const long long * __restrict__ audio_off,
+                             const long long * __restrict__ audio_len, const unsigned int * __restrict__ peak_bits,
+                             short * __restrict__ pcm) {
+    MIO_PDL_PROLOGUE();
+    const int utt = blockIdx.y;
+    const double peak = (double) __uint_as_float(peak_bits[utt]);
+    const bool scale = peak > 0.98;
+    const float gain = scale ? (float) (0.95 / peak) : 1.0f;
+    const float * p = audio + audio_off[utt];           // offsets are multiples of 64 samples
+    short * q = pcm + audio_off[utt];
+    const long long n = audio_len[utt], n4 = n >> 2;
+    auto cvt = [&](float x) {
+        if (scale) x = __fmul_rn(x, gain);
+        x = fminf(fmaxf(x, -1.0f), 1.0f);
+        return (short) __float2int_rn(__fmul_rn(x, 32767.0f));
+    };
+    const long long stride = (long long) gridDim.x * blockDim.x, t = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    for (long long i = t; i < n4; i += stride) {
+        const float4 v = reinterpret_cast<const float4 *>(p)[i];
+        short4 o;
+        o.x = cvt(v.x); o.y = cvt(v.y); o.z = cvt(v.z); o.w = cvt(v.w);
+        reinterpret_cast<short4 *>(q)[i] = o;
+    }
+    for (long long i = (n4 << 2) + t; i < n; i += stride) q[i] = cvt(p[i]);
+}
+
 // synthetic spectra for the iSTFT microbench (BASELINE config 3): log-magnitude ~ N(-2, 1), phase ~ U(-pi, pi)
 __device__ __forceinline__ unsigned long long splitmix64(unsigned long long x) {
     x += 0x9E3779B97F4A7C15ull;
@@ -434,6 +463,17 @@ void launch_peak_normalize(float * audio, const long long * audio_off, const lon
     if (bx > 1024) bx = 1024;
     dim3 grid((unsigned) bx, (unsigned) n_utt);
     launch_pdl(peak_normalize_kernel, dim3(grid), dim3(256), 0, st, audio, audio_off, audio_len, peak_bits);
+    MIO_CUDA(cudaGetLastError());
+    count_launch();
+}
+
+void launch_pcm16(const float * audio, const long long * audio_off, const long long * audio_len, const unsigned int * peak_bits,
+                  int16_t * pcm, int n_utt, long long max_len, cudaStream_t st) {
+    long long bx = (max_len / 4 + 255) / 256;
+    if (bx > 1024) bx = 1024;
+    if (bx < 1) bx = 1;
+    dim3 grid((unsigned) bx, (unsigned) n_utt);
+    launch_pdl(pcm16_kernel, dim3(grid), dim3(256), 0, st, audio, audio_off, audio_len, peak_bits, (short *) pcm);
     MIO_CUDA(cudaGetLastError());
     count_launch();
 }

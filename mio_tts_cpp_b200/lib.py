@@ -79,6 +79,12 @@ def load_library():
         "mio_tts_audio_free": (None, [fp]),
         "mio_tts_b200_synthesize_batch": (C.c_bool, [vp, C.POINTER(ip), szp, C.POINTER(fp), sz, sz, MioTtsParams,
                                                      fpp, szp, ip, cp, sz]),
+        "mio_tts_b200_synthesize_wav16_batch": (C.c_bool, [vp, C.POINTER(ip), szp, C.POINTER(fp), sz, sz, MioTtsParams,
+                                                           C.POINTER(C.POINTER(C.c_uint8)), szp, ip, cp, sz]),
+        "mio_tts_b200_wav_free": (None, [C.POINTER(C.c_uint8)]),
+        "mio_tts_b200_context_enable_batching": (C.c_bool, [vp, i32, i32, i32, cp, sz]),
+        "mio_tts_b200_batching_stats": (C.c_bool, [vp, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]),
+        "mio_tts_b200_audio_to_pcm16": (C.c_bool, [vp, C.POINTER(fp), szp, sz, C.POINTER(C.POINTER(C.c_int16)), cp, sz]),
         "mio_tts_b200_decode_spec": (C.c_bool, [vp, ip, sz, fp, sz, fpp, ip, ip, cp, sz]),
         "mio_tts_b200_debug_stage": (C.c_bool, [vp, ip, sz, fp, sz, i32, fpp, ip, ip, cp, sz]),
         "mio_tts_b200_gather": (C.c_bool, [vp, ip, sz, fp, cp, sz]),
@@ -221,6 +227,43 @@ class MioTTS:
             res.append(a.copy() if copy else int(ns[i]))
             self.L.mio_tts_audio_free(outs[i])
         return res, sr.value
+
+    def synthesize_wav16_batch(self, codes_list, emb_list, copy=True):
+        """mio_tts_b200_synthesize_wav16_batch.  Returns a list of `bytes` (44-byte RIFF/WAVE header + int16 PCM)."""
+        B, codes, cp, cn, embs, ep, n_emb = self._batch_args(codes_list, emb_list)
+        outs = (C.POINTER(C.c_uint8) * B)()
+        ns = (C.c_size_t * B)()
+        ok = self.L.mio_tts_b200_synthesize_wav16_batch(self.ctx, cp, cn, ep, n_emb, B, self.default_params(), outs, ns, None,
+                                                        self._err, ERR_SIZE)
+        self._check(ok)
+        res = []
+        for i in range(B):
+            res.append(C.string_at(outs[i], ns[i]) if copy else int(ns[i]))
+            self.L.mio_tts_b200_wav_free(outs[i])
+        return res
+
+    def pcm16_from_audio(self, audio_list):
+        arrs = [_f32(a) for a in audio_list]
+        b = len(arrs)
+        ptrs = (C.POINTER(C.c_float) * b)(*[_ptr(a, C.c_float) for a in arrs])
+        ns = (C.c_size_t * b)(*[a.size for a in arrs])
+        outs = (C.POINTER(C.c_int16) * b)()
+        self._check(self.L.mio_tts_b200_audio_to_pcm16(self.ctx, ptrs, ns, b, outs, self._err, ERR_SIZE))
+        res = []
+        for i in range(b):
+            res.append(np.ctypeslib.as_array(outs[i], shape=(arrs[i].size,)).copy())
+            self.L.mio_tts_b200_free(outs[i])
+        return res
+
+    def enable_batching(self, max_batch=64, max_wait_us=300, workers=2):
+        """Micro-batcher for concurrent mio_tts_synthesize calls on this context and its later clones (max_batch <= 0: off)."""
+        self._check(self.L.mio_tts_b200_context_enable_batching(self.ctx, max_batch, max_wait_us, workers, self._err, ERR_SIZE))
+
+    def batching_stats(self):
+        v = [C.c_uint64(0) for _ in range(4)]
+        if not self.L.mio_tts_b200_batching_stats(self.ctx, *[C.byref(x) for x in v]):
+            return None
+        return dict(zip(("requests", "batches", "largest", "retried_single"), [int(x.value) for x in v]))
 
     # ---- stage hooks ----------------------------------------------------------------------------------
     def decode_spec(self, codes, embedding):
