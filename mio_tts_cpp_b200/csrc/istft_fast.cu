@@ -12,6 +12,9 @@
 //   * the steady-state envelope (sum of hann^2 over the 4 overlapping frames) is tabulated once per CTA.
 #include "common.h"
 
+#include <type_traits>
+#include <utility>
+
 namespace mio {
 namespace {
 
@@ -64,19 +67,79 @@ template <int R> __device__ __forceinline__ void dft_small(float2 (&v)[R]) {   /
     }
 }
 
-// one in-place Stockham pass by one warp (reads x[j + q*m], writes x[(j-k)*R + k + p*Ls], k = j % Ls)
-template <int M, int R, int LS>
+// ---- compile-time loops (indices must be constant expressions so the small-DFT twiddles fold into immediates) ----
+template <int... I, typename F>
+__device__ __forceinline__ void static_for_impl(std::integer_sequence<int, I...>, F && f) { (f(std::integral_constant<int, I>{}), ...); }
+template <int N, typename F> __device__ __forceinline__ void static_for(F && f) { static_for_impl(std::make_integer_sequence<int, N>{}, f); }
+
+template <int R> struct root_tab;      // e^{+2 pi i a / R}, a = 0..R-1
+template <> struct root_tab<16> {
+    static constexpr float c[16] = {1.0f, 0.923879533f, 0.707106781f, 0.382683432f, 0.0f, -0.382683432f, -0.707106781f, -0.923879533f, -1.0f, -0.923879533f, -0.707106781f, -0.382683432f, 0.0f, 0.382683432f, 0.707106781f, 0.923879533f};
+    static constexpr float s[16] = {0.0f, 0.382683432f, 0.707106781f, 0.923879533f, 1.0f, 0.923879533f, 0.707106781f, 0.382683432f, 0.0f, -0.382683432f, -0.707106781f, -0.923879533f, -1.0f, -0.923879533f, -0.707106781f, -0.382683432f};
+};
+template <> struct root_tab<15> {
+    static constexpr float c[15] = {1.0f, 0.913545458f, 0.669130606f, 0.309016994f, -0.104528463f, -0.5f, -0.809016994f, -0.978147601f, -0.978147601f, -0.809016994f, -0.5f, -0.104528463f, 0.309016994f, 0.669130606f, 0.913545458f};
+    static constexpr float s[15] = {0.0f, 0.406736643f, 0.743144825f, 0.951056516f, 0.994521895f, 0.866025404f, 0.587785252f, 0.207911691f, -0.207911691f, -0.587785252f, -0.866025404f, -0.994521895f, -0.951056516f, -0.743144825f, -0.406736643f};
+};
+template <> struct root_tab<10> {
+    static constexpr float c[10] = {1.0f, 0.809016994f, 0.309016994f, -0.309016994f, -0.809016994f, -1.0f, -0.809016994f, -0.309016994f, 0.309016994f, 0.809016994f};
+    static constexpr float s[10] = {0.0f, 0.587785252f, 0.951056516f, 0.951056516f, 0.587785252f, 0.0f, -0.587785252f, -0.951056516f, -0.951056516f, -0.587785252f};
+};
+
+// DFT of composite size R1*R2 in registers (Cooley-Tukey, natural order in and out):
+//   X[k1 + R1 k2] = sum_n2 W_R^{n2 k1} W_R2^{n2 k2} sum_n1 x[n2 + R2 n1] W_R1^{n1 k1}
+template <int R1, int R2> __device__ __forceinline__ void dft_ct(float2 (&v)[R1 * R2]) {
+    constexpr int R = R1 * R2;
+    float2 y[R2][R1];
+    static_for<R2>([&](auto N2) {
+        constexpr int n2 = decltype(N2)::value;
+        float2 t[R1];
+        static_for<R1>([&](auto N1) { constexpr int n1 = decltype(N1)::value; t[n1] = v[n2 + R2 * n1]; });
+        dft_small<R1>(t);
+        static_for<R1>([&](auto K1) {
+            constexpr int k1 = decltype(K1)::value;
+            constexpr int a = (n2 * k1) % R;
+            constexpr float wc = root_tab<R>::c[a], ws = root_tab<R>::s[a];   // folded by the front end: immediates
+            if constexpr (a == 0) y[n2][k1] = t[k1];
+            else y[n2][k1] = cmul(t[k1], make_float2(wc, ws));
+        });
+    });
+    static_for<R1>([&](auto K1) {
+        constexpr int k1 = decltype(K1)::value;
+        float2 u[R2];
+        static_for<R2>([&](auto N2) { constexpr int n2 = decltype(N2)::value; u[n2] = y[n2][k1]; });
+        dft_small<R2>(u);
+        static_for<R2>([&](auto K2) { constexpr int k2 = decltype(K2)::value; v[k1 + R1 * k2] = u[k2]; });
+    });
+}
+
+template <int R> __device__ __forceinline__ void dft_any(float2 (&v)[R]) {
+    if constexpr (R <= 5) dft_small<R>(v);
+    else if constexpr (R == 16) dft_ct<4, 4>(v);
+    else if constexpr (R == 15) dft_ct<3, 5>(v);
+    else { static_assert(R == 10, "radix"); dft_ct<2, 5>(v); }
+}
+
+// Shared-memory index of complex element i while a frame is between passes: one pad slot per 16 elements, so the
+// stride-R stores of the first pass (and the stride-16 ones after it) fall on distinct banks.
+__device__ __forceinline__ int padi(int i) { return i + (i >> 4); }
+template <int M> struct padded_len { static constexpr int value = M + (M >> 4); };
+
+// One in-place Stockham pass by one warp: reads x[j + q*m] (q < R), writes x[(j-k)*R + k + p*Ls], k = j % Ls.
+// All inputs of the pass sit in registers before the first store, so the pass runs in place; the LAST pass stores to
+// the un-padded (linear) positions, which is what the overlap-add reads with 16-byte loads.
+// tw: this pass's twiddles, compact and conflict-free: tw[(q-1)*Ls + k] = W_{Ls*R}^{q k}.
+template <int M, int R, int LS, bool LAST>
 __device__ __forceinline__ void pass_inplace(float2 * buf, const float2 * tw, int lane) {
     constexpr int m = M / R;
     constexpr int B = (m + 31) / 32;
-    constexpr int TS = M / (LS * R);
     float2 v[B][R];
 #pragma unroll
     for (int i = 0; i < B; ++i) {
         const int j = lane + 32 * i;
         if (j < m) {
 #pragma unroll
-            for (int q = 0; q < R; ++q) v[i][q] = buf[j + q * m];
+            for (int q = 0; q < R; ++q) v[i][q] = buf[padi(j + q * m)];
         }
     }
     __syncwarp();
@@ -87,12 +150,15 @@ __device__ __forceinline__ void pass_inplace(float2 * buf, const float2 * tw, in
             const int k = j % LS;
             if constexpr (LS > 1) {
 #pragma unroll
-                for (int q = 1; q < R; ++q) v[i][q] = cmul(v[i][q], tw[q * k * TS]);
+                for (int q = 1; q < R; ++q) v[i][q] = cmul(v[i][q], tw[(q - 1) * LS + k]);
             }
-            dft_small<R>(v[i]);
+            dft_any<R>(v[i]);
             const int base = (j - k) * R + k;
 #pragma unroll
-            for (int p = 0; p < R; ++p) buf[base + p * LS] = v[i][p];
+            for (int p = 0; p < R; ++p) {
+                const int idx = base + p * LS;
+                buf[LAST ? idx : padi(idx)] = v[i][p];
+            }
         }
     }
     __syncwarp();
@@ -101,8 +167,26 @@ __device__ __forceinline__ void pass_inplace(float2 * buf, const float2 * tw, in
 template <int M, int LS> __device__ __forceinline__ void run_passes(float2 *, const float2 *, int) {}
 template <int M, int LS, int R, int... Rest>
 __device__ __forceinline__ void run_passes(float2 * buf, const float2 * tw, int lane) {
-    pass_inplace<M, R, LS>(buf, tw, lane);
-    run_passes<M, LS * R, Rest...>(buf, tw, lane);
+    pass_inplace<M, R, LS, sizeof...(Rest) == 0>(buf, tw, lane);
+    run_passes<M, LS * R, Rest...>(buf, tw + (LS > 1 ? (R - 1) * LS : 0), lane);
+}
+
+// per-pass twiddle tables, laid out in pass order (the first pass has none)
+template <int M, int LS, int... Rs> struct tw_table_len { static constexpr int value = 0; };
+template <int M, int LS, int R, int... Rest> struct tw_table_len<M, LS, R, Rest...> {
+    static constexpr int value = (LS > 1 ? (R - 1) * LS : 0) + tw_table_len<M, LS * R, Rest...>::value;
+};
+template <int M, int LS> __device__ __forceinline__ void fill_tw(float2 *, const float2 *, int, int) {}
+template <int M, int LS, int R, int... Rest>
+__device__ __forceinline__ void fill_tw(float2 * dst, const float2 * __restrict__ tw_m, int tid, int nthreads) {
+    if constexpr (LS > 1) {
+        constexpr int TS = M / (LS * R);
+        for (int e = tid; e < (R - 1) * LS; e += nthreads) {
+            const int q = e / LS + 1, k = e - (q - 1) * LS;
+            dst[e] = tw_m[q * k * TS];
+        }
+    }
+    fill_tw<M, LS * R, Rest...>(dst + (LS > 1 ? (R - 1) * LS : 0), tw_m, tid, nthreads);
 }
 
 // X_k = min(exp(logmag), 100) * (cos phi, sin phi) on the SFU
@@ -119,13 +203,15 @@ __device__ __forceinline__ float2 polar_fast(float logmag, float phase) {
 template <int N, int... RADIX>
 __global__ void __launch_bounds__(FTHREADS, 1) istft_fast_kernel(const fast_params P) {
     MIO_PDL_PROLOGUE();
-    constexpr int M = N / 2, H = N / 4, CARRY = N - H, SPAN = FW * H;
+    constexpr int M = N / 2, H = N / 4, CARRY = N - H, SPAN = FW * H, MP = padded_len<M>::value;
+    constexpr int TWL = tw_table_len<M, 1, RADIX...>::value;
+    static_assert(H % 4 == 0 && MP % 2 == 0, "16-byte rows");
     extern __shared__ __align__(16) uint8_t smem[];
-    float2 * s_twm = reinterpret_cast<float2 *>(smem);                 // [M]
-    float2 * s_twn = s_twm + M;                                         // [M/2 + 1]
-    float2 * s_buf = s_twn + (M / 2 + 1);                               // [FW][M]
-    float * s_hann = reinterpret_cast<float *>(s_buf + (size_t) FW * M);   // [N]
-    float * s_env = s_hann + N;                                         // [H]
+    float2 * s_buf = reinterpret_cast<float2 *>(smem);                  // [FW][MP]
+    float2 * s_tw = s_buf + (size_t) FW * MP;                           // per-pass twiddles
+    float2 * s_twn = s_tw + TWL;                                        // [M/2 + 1]
+    float * s_hs = reinterpret_cast<float *>(s_twn + (M / 2 + 2));      // [N]  hann * 1/n_freq
+    float * s_env = s_hs + N;                                           // [H]
     float * s_carry = s_env + H;                                        // [2][CARRY]
     float * s_xm = s_carry + 2 * CARRY;                                 // [FW]
     int * s_valid = reinterpret_cast<int *>(s_xm + FW);                 // [FW]
@@ -140,15 +226,14 @@ __global__ void __launch_bounds__(FTHREADS, 1) istft_fast_kernel(const fast_para
     const long long out_len = n_full - 2 * P.pad;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int i = threadIdx.x; i < M; i += FTHREADS) s_twm[i] = P.tw_m[i];
+    fill_tw<M, 1, RADIX...>(s_tw, P.tw_m, threadIdx.x, FTHREADS);
     for (int i = threadIdx.x; i <= M / 2; i += FTHREADS) s_twn[i] = P.tw_n[i];
-    for (int i = threadIdx.x; i < N; i += FTHREADS) s_hann[i] = P.hann[i];
+    for (int i = threadIdx.x; i < N; i += FTHREADS) s_hs[i] = P.hann[i] * P.scale;
     for (int i = threadIdx.x; i < 2 * CARRY; i += FTHREADS) s_carry[i] = 0.0f;
-    __syncthreads();
     for (int r = threadIdx.x; r < H; r += FTHREADS) {   // 4 overlapping frames, ascending frame = descending offset
         float e = 0.0f;
 #pragma unroll
-        for (int q = 3; q >= 0; --q) { const float hv = s_hann[r + q * H]; e += hv * hv; }
+        for (int q = 3; q >= 0; --q) { const float hv = P.hann[r + q * H]; e += hv * hv; }
         s_env[r] = e;
     }
 
@@ -156,7 +241,7 @@ __global__ void __launch_bounds__(FTHREADS, 1) istft_fast_kernel(const fast_para
     long long ll = (b - 1) / H;
     if (ll > S - 1) ll = S - 1;
 
-    float2 * buf = s_buf + (size_t) warp * M;
+    float2 * buf = s_buf + (size_t) warp * MP;
     const float * spec_u = P.spec + (size_t) P.spec_row0[utt] * P.pitch;
     float * audio_u = P.audio + P.audio_off[utt];
     float peak = 0.0f;
@@ -186,56 +271,70 @@ __global__ void __launch_bounds__(FTHREADS, 1) istft_fast_kernel(const fast_para
                         const float2 B2 = cmul(X2, make_float2(-w.x, w.y));
                         const float2 E = make_float2(0.5f * (Xk.x + X2.x), 0.5f * (Xk.y - X2.y));
                         const float2 O = make_float2(0.5f * (Bk.x + B2.x), 0.5f * (Bk.y - B2.y));
-                        buf[k] = make_float2(E.x - O.y, E.y + O.x);
-                        if (k2 != k) buf[k2] = make_float2(E.x + O.y, O.x - E.y);
+                        buf[padi(k)] = make_float2(E.x - O.y, E.y + O.x);
+                        if (k2 != k) buf[padi(k2)] = make_float2(E.x + O.y, O.x - E.y);
                     }
                 }
             }
             __syncwarp();
-            run_passes<M, 1, RADIX...>(buf, s_twm, lane);
+            run_passes<M, 1, RADIX...>(buf, s_tw, lane);
         }
         if (lane == 0) s_valid[warp] = valid ? 1 : 0;
         __syncthreads();
 
-        // ---------------- phase 2: overlap-add the round, emit finished samples ----------------
+        // ---------------- phase 2: overlap-add the round four samples at a time, emit finished samples ----------------
         const long long base = lr0 * H;
         const float * carry_in = s_carry + cur * CARRY;
         float * carry_out = s_carry + (cur ^ 1) * CARRY;
-        for (int x = threadIdx.x; x < SPAN + CARRY; x += FTHREADS) {
+        for (int x4 = threadIdx.x; x4 < (SPAN + CARRY) / 4; x4 += FTHREADS) {
+            const int x = x4 * 4;
             const bool to_carry = x >= SPAN;
-            float acc = (!to_carry && x < CARRY) ? carry_in[x] : 0.0f;
+            float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            if (!to_carry && x < CARRY) acc = *reinterpret_cast<const float4 *>(carry_in + x);
             const int q = x / H;
             const int w_lo = q - 3 > 0 ? q - 3 : 0;
             const int w_hi = q < FW - 1 ? q : FW - 1;
-            for (int w = w_lo; w <= w_hi; ++w) {
+            for (int w = w_lo; w <= w_hi; ++w) {      // ascending frame, like the reference's accumulation order
                 if (s_valid[w] == 0) continue;
                 const int t = x - w * H;
-                const float * zf = reinterpret_cast<const float *>(s_buf + (size_t) w * M);
+                const float4 z = *reinterpret_cast<const float4 *>(reinterpret_cast<const float *>(s_buf + (size_t) w * MP) + t);
+                const float4 hs = *reinterpret_cast<const float4 *>(s_hs + t);
                 const float xm = s_xm[w];
-                const float yv = (zf[t] + ((t & 1) ? -xm : xm)) * P.scale;
-                acc += yv * s_hann[t];
+                acc.x = fmaf(z.x + xm, hs.x, acc.x);
+                acc.y = fmaf(z.y - xm, hs.y, acc.y);
+                acc.z = fmaf(z.z + xm, hs.z, acc.z);
+                acc.w = fmaf(z.w - xm, hs.w, acc.w);
             }
             if (to_carry) {
-                carry_out[x - SPAN] = acc;
+                *reinterpret_cast<float4 *>(carry_out + (x - SPAN)) = acc;
             } else {
                 const long long i = base + x;
                 const long long o = i - P.pad;
                 if (i >= a && i < b && o >= 0 && o < out_len) {
-                    const long long fi = i / H;
-                    float env;
+                    const int fi = (int) (lr0 + q);           // hop index of these four samples
+                    const int r = x - q * H;
+                    float4 env;
                     if (fi >= 3 && fi <= S - 1) {
-                        env = s_env[(int) (i - fi * H)];
+                        env = *reinterpret_cast<const float4 *>(s_env + r);
                     } else {
-                        const long long e_lo = fi - 3 > 0 ? fi - 3 : 0;
-                        const long long e_hi = fi < S - 1 ? fi : S - 1;
-                        env = 0.0f;
-                        for (long long f = e_lo; f <= e_hi; ++f) { const float hv = s_hann[(int) (i - f * H)]; env += hv * hv; }
+                        const int e_lo = fi - 3 > 0 ? fi - 3 : 0;
+                        const int e_hi = fi < S - 1 ? fi : S - 1;
+                        float e[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+                        for (int f = e_lo; f <= e_hi; ++f) {
+#pragma unroll
+                            for (int c = 0; c < 4; ++c) { const float hv = P.hann[r + c + (fi - f) * H]; e[c] += hv * hv; }
+                        }
+                        env = make_float4(e[0], e[1], e[2], e[3]);
                     }
-                    float yv = acc;
-                    if (env > 1e-12f) yv /= env;
-                    audio_u[o] = yv;
-                    const float av = fabsf(yv);
-                    if (av <= 3.402823466e38f) peak = fmaxf(peak, av);
+                    float4 y = acc;
+                    if (env.x > 1e-12f) y.x /= env.x;
+                    if (env.y > 1e-12f) y.y /= env.y;
+                    if (env.z > 1e-12f) y.z /= env.z;
+                    if (env.w > 1e-12f) y.w /= env.w;
+                    *reinterpret_cast<float4 *>(audio_u + o) = y;
+                    const float av[4] = {fabsf(y.x), fabsf(y.y), fabsf(y.z), fabsf(y.w)};
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) if (av[c] <= 3.402823466e38f) peak = fmaxf(peak, av[c]);
                 }
             }
         }
@@ -251,17 +350,34 @@ __global__ void __launch_bounds__(FTHREADS, 1) istft_fast_kernel(const fast_para
 }
 
 template <int N, int... RADIX>
-void launch_fast_t(const fast_params & P, int n_utt, int max_frames, cudaStream_t st) {
-    constexpr int M = N / 2, H = N / 4;
-    const size_t smem = (size_t) M * 8 + (size_t) (M / 2 + 1) * 8 + (size_t) FW * M * 8 + (size_t) N * 4 + (size_t) H * 4 +
+void launch_fast_t(fast_params P, const int * h_frames, int n_utt, int max_frames, cudaStream_t st) {
+    constexpr int M = N / 2, H = N / 4, MP = padded_len<M>::value;
+    constexpr int TWL = tw_table_len<M, 1, RADIX...>::value;
+    const size_t smem = (size_t) FW * MP * 8 + (size_t) TWL * 8 + (size_t) (M / 2 + 2) * 8 + (size_t) N * 4 + (size_t) H * 4 +
                         (size_t) 2 * (N - H) * 4 + FW * 8 + 64;
     static bool configured[64] = {false};
+    static int n_sm[64] = {0};
     int dev = 0;
     MIO_CUDA(cudaGetDevice(&dev));
     if (!configured[dev & 63]) {
         MIO_CUDA(cudaFuncSetAttribute(istft_fast_kernel<N, RADIX...>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        MIO_CUDA(cudaDeviceGetAttribute(&n_sm[dev & 63], cudaDevAttrMultiProcessorCount, dev));
         configured[dev & 63] = true;
     }
+    // Chunk length = rounds of FW frames minus the 3 halo frames a chunk recomputes.  One CTA per SM: pick the round
+    // count whose CTA total wastes the least in the last wave (cost = waves * rounds).
+    const int sms = std::max(1, n_sm[dev & 63]);
+    long long best_cost = -1;
+    int best_rounds = 4;
+    for (int rounds = 2; rounds <= 10; ++rounds) {
+        const int fpc = rounds * FW - 3;
+        long long ctas = 0;
+        if (h_frames) for (int u = 0; u < n_utt; ++u) ctas += ((long long) h_frames[u] + 3 + fpc - 1) / fpc;
+        else ctas = (long long) n_utt * ((max_frames + 3 + fpc - 1) / fpc);
+        const long long cost = ((ctas + sms - 1) / sms) * rounds;
+        if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_rounds = rounds; }
+    }
+    P.frames_per_chunk = best_rounds * FW - 3;
     const long long n_full_max = (long long) (max_frames - 1) * H + N;
     const long long chunk = (long long) P.frames_per_chunk * H;
     dim3 grid((unsigned) ((n_full_max + chunk - 1) / chunk), (unsigned) n_utt);
@@ -287,9 +403,9 @@ bool launch_istft_fast(const istft_plan & p, const float * spec, int pitch, cons
     P.audio_off = audio_off; P.audio = audio; P.peak_bits = peak_bits;
     P.scale = 1.0f / (float) P.n_freq;
     switch (p.n_fft) {
-        case 1920: launch_fast_t<1920, 4, 4, 4, 3, 5>(P, n_utt, max_frames, st); break;
-        case 2048: launch_fast_t<2048, 4, 4, 4, 4, 4>(P, n_utt, max_frames, st); break;
-        default: launch_fast_t<1280, 4, 4, 4, 2, 5>(P, n_utt, max_frames, st); break;
+        case 1920: launch_fast_t<1920, 16, 15, 4>(P, nullptr, n_utt, max_frames, st); break;
+        case 2048: launch_fast_t<2048, 16, 16, 4>(P, nullptr, n_utt, max_frames, st); break;
+        default: launch_fast_t<1280, 16, 10, 4>(P, nullptr, n_utt, max_frames, st); break;
     }
     return true;
 }
