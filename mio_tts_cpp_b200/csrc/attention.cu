@@ -86,47 +86,57 @@ __global__ void __launch_bounds__(128) attention_band_kernel(const uint16_t * __
     const int g = lane >> 2, tq = lane & 3;
     const int q0 = warp * 16;          // first query of this warp; its keys are indices [q0, q0 + 80)
 
-    // ---- S = Q K^T (16 x 80) ----
+    // ---- S = Q K^T (16 x 80); A and B fragments through ldmatrix (4 + 20 instructions instead of 96 scalar loads) ----
+    const int mi = lane >> 3, mr = lane & 7;
     uint32_t qa[4][4];
 #pragma unroll
     for (int kk = 0; kk < 4; ++kk) {
-        const uint16_t * base = Qs + (q0 + g) * LDS + kk * 16 + 2 * tq;
-        qa[kk][0] = *reinterpret_cast<const uint32_t *>(base);
-        qa[kk][1] = *reinterpret_cast<const uint32_t *>(base + 8 * LDS);
-        qa[kk][2] = *reinterpret_cast<const uint32_t *>(base + 8);
-        qa[kk][3] = *reinterpret_cast<const uint32_t *>(base + 8 * LDS + 8);
+        const uint32_t addr = (uint32_t) __cvta_generic_to_shared(Qs + (q0 + (mi & 1) * 8 + mr) * LDS + kk * 16 + (mi >> 1) * 8);
+        asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(qa[kk][0]), "=r"(qa[kk][1]), "=r"(qa[kk][2]), "=r"(qa[kk][3]) : "r"(addr));
     }
     float s[10][4];
 #pragma unroll
     for (int nt = 0; nt < 10; ++nt) {
         s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.0f;
-        const uint16_t * kb = Ks + (q0 + nt * 8 + g) * LDS + 2 * tq;
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk) {
-            const uint32_t b0 = *reinterpret_cast<const uint32_t *>(kb + kk * 16);
-            const uint32_t b1 = *reinterpret_cast<const uint32_t *>(kb + kk * 16 + 8);
-            mma16816<BF16>(s[nt], qa[kk], b0, b1);
+        for (int kp = 0; kp < 2; ++kp) {      // head-dim columns [32 kp, 32 kp + 32): fragments (b0, b1) of kk = 2 kp and 2 kp + 1
+            const uint32_t addr = (uint32_t) __cvta_generic_to_shared(Ks + (q0 + nt * 8 + mr) * LDS + kp * 32 + mi * 8);
+            uint32_t b0, b1, b2, b3;
+            asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(b0), "=r"(b1), "=r"(b2), "=r"(b3) : "r"(addr));
+            mma16816<BF16>(s[nt], qa[2 * kp], b0, b1);
+            mma16816<BF16>(s[nt], qa[2 * kp + 1], b2, b3);
         }
     }
 
     // ---- band mask + softmax (rows g and g+8 of this warp's 16 queries) ----
+    // In warp-local key index jj = nt*8 + 2*tq + e (key position kpos0 + q0 + jj), row r of the warp sees
+    // jj in [r + 32 - hw, r + 32 + hw], clipped to the utterance: one unsigned compare per element.
     const int qi0 = q0 + g, qi1 = q0 + g + 8;             // query index in tile
-    const int qp0 = t.pos0 + qi0, qp1 = t.pos0 + qi1;     // positions
     const bool qv0 = qi0 < t.n, qv1 = qi1 < t.n;
+    const int j_min = -(kpos0 + q0), j_max = t.utt_len - 1 - kpos0 - q0;
+    int lo0 = max(g + 32 - half_window, j_min), hi0 = min(g + 32 + half_window, j_max);
+    int lo1 = max(g + 40 - half_window, j_min), hi1 = min(g + 40 + half_window, j_max);
+    if (!qv0 || hi0 < lo0) { lo0 = 1 << 20; hi0 = lo0; }
+    if (!qv1 || hi1 < lo1) { lo1 = 1 << 20; hi1 = lo1; }
+    const unsigned span0 = (unsigned) (hi0 - lo0), span1 = (unsigned) (hi1 - lo1);
+    const int d0 = 2 * tq - lo0, d1 = 2 * tq - lo1;
+    // full 65-wide window, all 16 queries present, no utterance edge inside the 80 keys: tiles 2..7 are unmasked
+    const bool interior = half_window == 32 && j_min <= 0 && j_max >= 79 && q0 + 15 < t.n;
     float m0 = -INFINITY, m1 = -INFINITY;
 #pragma unroll
     for (int nt = 0; nt < 10; ++nt) {
+        if (nt < 2 || nt > 7 || !interior) {
 #pragma unroll
-        for (int e = 0; e < 2; ++e) {
-            const int kp = kpos0 + q0 + nt * 8 + 2 * tq + e;
-            const bool kvld = kp >= 0 && kp < t.utt_len;
-            const bool ok0 = qv0 && kvld && abs(kp - qp0) <= half_window;
-            const bool ok1 = qv1 && kvld && abs(kp - qp1) <= half_window;
-            s[nt][e] = ok0 ? s[nt][e] : -INFINITY;
-            s[nt][2 + e] = ok1 ? s[nt][2 + e] : -INFINITY;
-            m0 = fmaxf(m0, s[nt][e]);
-            m1 = fmaxf(m1, s[nt][2 + e]);
+            for (int e = 0; e < 2; ++e) {
+                const int c = nt * 8 + e;
+                s[nt][e] = (unsigned) (c + d0) <= span0 ? s[nt][e] : -INFINITY;
+                s[nt][2 + e] = (unsigned) (c + d1) <= span1 ? s[nt][2 + e] : -INFINITY;
+            }
         }
+        m0 = fmaxf(m0, fmaxf(s[nt][0], s[nt][1]));
+        m1 = fmaxf(m1, fmaxf(s[nt][2], s[nt][3]));
     }
     m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1));
     m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
@@ -161,7 +171,6 @@ __global__ void __launch_bounds__(128) attention_band_kernel(const uint16_t * __
         pa[1] = pack2<BF16>(s[2 * kk][2], s[2 * kk][3]);
         pa[2] = pack2<BF16>(s[2 * kk + 1][0], s[2 * kk + 1][1]);
         pa[3] = pack2<BF16>(s[2 * kk + 1][2], s[2 * kk + 1][3]);
-        const int mi = lane >> 3, mr = lane & 7;
         const int key = q0 + kk * 16 + (mi & 1) * 8 + mr;
 #pragma unroll
         for (int nd = 0; nd < 8; nd += 2) {
@@ -175,17 +184,23 @@ __global__ void __launch_bounds__(128) attention_band_kernel(const uint16_t * __
         }
     }
 
-    const float inv0 = l0 > 0.0f ? 1.0f / l0 : 0.0f;
-    const float inv1 = l1 > 0.0f ? 1.0f / l1 : 0.0f;
+    // ---- normalise, stage the warp's 16 x 64 tile in its own (now dead) Q rows, store 128-byte rows coalesced ----
+    const float inv0 = l0 > 0.0f ? __fdividef(1.0f, l0) : 0.0f;
+    const float inv1 = l1 > 0.0f ? __fdividef(1.0f, l1) : 0.0f;
+    __syncwarp();
 #pragma unroll
     for (int nd = 0; nd < 8; ++nd) {
-        const int col = head * HD + nd * 8 + 2 * tq;
-        if (qv0)
-            *reinterpret_cast<uint32_t *>(out + (size_t) (t.row0 + qi0) * dim + col) =
-                pack2<BF16>(o[nd][0] * inv0, o[nd][1] * inv0);
-        if (qv1)
-            *reinterpret_cast<uint32_t *>(out + (size_t) (t.row0 + qi1) * dim + col) =
-                pack2<BF16>(o[nd][2] * inv1, o[nd][3] * inv1);
+        *reinterpret_cast<uint32_t *>(Qs + qi0 * LDS + nd * 8 + 2 * tq) = pack2<BF16>(o[nd][0] * inv0, o[nd][1] * inv0);
+        *reinterpret_cast<uint32_t *>(Qs + qi1 * LDS + nd * 8 + 2 * tq) = pack2<BF16>(o[nd][2] * inv1, o[nd][3] * inv1);
+    }
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int c = lane + 32 * i, row = q0 + (c >> 3), ch = c & 7;
+        if (row < t.n) {
+            const uint4 v = *reinterpret_cast<const uint4 *>(Qs + row * LDS + ch * 8);
+            *reinterpret_cast<uint4 *>(out + (size_t) (t.row0 + row) * dim + head * HD + ch * 8) = v;
+        }
     }
 }
 

@@ -32,10 +32,32 @@ struct fast_params {
     float scale;
 };
 
-__device__ __forceinline__ float2 cmul(float2 a, float2 b) { return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
-__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
-__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+// ---- complex arithmetic on the packed fp32x2 pipe (FADD2 / FMUL2 / FFMA2, sm_100): one instruction per complex add and
+// two per complex multiply; ptxas folds the pack / swap / broadcast / negate below into operand modifiers
+// (.F32x2.LO_HI.NP, .F32), so the helpers cost nothing beyond the arithmetic itself.
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pk2(float lo, float hi) { u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ float2 up2(u64 v) { float2 r; asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v)); return r; }
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) {
+    u64 d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(pk2(a.x, a.y)), "l"(pk2(b.x, b.y))); return up2(d);
+}
+__device__ __forceinline__ float2 csub(float2 a, float2 b) {
+    u64 d; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(pk2(a.x, a.y)), "l"(pk2(b.x, b.y))); return up2(d);
+}
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) {
+    u64 d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(pk2(a.x, a.y)), "l"(pk2(b.x, b.y))); return up2(d);
+}
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) {
+    u64 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(pk2(a.x, a.y)), "l"(pk2(b.x, b.y)), "l"(pk2(c.x, c.y))); return up2(d);
+}
 __device__ __forceinline__ float2 cmul_i(float2 a) { return make_float2(-a.y, a.x); }
+__device__ __forceinline__ float2 bc(float s) { return make_float2(s, s); }
+// a * w = a.x * (w.x, w.y) + a.y * (-w.y, w.x)
+__device__ __forceinline__ float2 cmul(float2 a, float2 w) { return fma2(bc(a.y), make_float2(-w.y, w.x), mul2(bc(a.x), w)); }
+// the same with the rotated twiddle already in the table: W = (w.x, w.y, -w.y, w.x)
+__device__ __forceinline__ float2 cmul_pre(float2 a, float4 W) {
+    return fma2(bc(a.y), make_float2(W.z, W.w), mul2(bc(a.x), make_float2(W.x, W.y)));
+}
 
 template <int R> __device__ __forceinline__ void dft_small(float2 (&v)[R]) {   // inverse kernel e^{+2 pi i p q / R}
     if constexpr (R == 2) {
@@ -48,8 +70,8 @@ template <int R> __device__ __forceinline__ void dft_small(float2 (&v)[R]) {   /
     } else if constexpr (R == 3) {
         const float s3 = 0.86602540378443864676f;
         const float2 s = cadd(v[1], v[2]), d = csub(v[1], v[2]);
-        const float2 m = make_float2(v[0].x - 0.5f * s.x, v[0].y - 0.5f * s.y);
-        const float2 id = make_float2(-s3 * d.y, s3 * d.x);
+        const float2 m = fma2(bc(-0.5f), s, v[0]);
+        const float2 id = mul2(bc(s3), cmul_i(d));
         v[0] = cadd(v[0], s); v[1] = cadd(m, id); v[2] = csub(m, id);
     } else {
         static_assert(R == 5, "radix");
@@ -57,13 +79,13 @@ template <int R> __device__ __forceinline__ void dft_small(float2 (&v)[R]) {   /
         const float s1 = 0.95105651629515357212f, s2 = 0.58778525229247312917f;
         const float2 a1 = cadd(v[1], v[4]), a2 = cadd(v[2], v[3]);
         const float2 b1 = csub(v[1], v[4]), b2 = csub(v[2], v[3]);
-        const float2 m1 = make_float2(v[0].x + c1 * a1.x + c2 * a2.x, v[0].y + c1 * a1.y + c2 * a2.y);
-        const float2 m2 = make_float2(v[0].x + c2 * a1.x + c1 * a2.x, v[0].y + c2 * a1.y + c1 * a2.y);
-        const float2 n1 = make_float2(s1 * b1.x + s2 * b2.x, s1 * b1.y + s2 * b2.y);
-        const float2 n2 = make_float2(s2 * b1.x - s1 * b2.x, s2 * b1.y - s1 * b2.y);
+        const float2 m1 = fma2(bc(c2), a2, fma2(bc(c1), a1, v[0]));
+        const float2 m2 = fma2(bc(c1), a2, fma2(bc(c2), a1, v[0]));
+        const float2 n1 = cmul_i(fma2(bc(s2), b2, mul2(bc(s1), b1)));
+        const float2 n2 = cmul_i(fma2(bc(-s1), b2, mul2(bc(s2), b1)));
         v[0] = cadd(v[0], cadd(a1, a2));
-        v[1] = cadd(m1, cmul_i(n1)); v[4] = csub(m1, cmul_i(n1));
-        v[2] = cadd(m2, cmul_i(n2)); v[3] = csub(m2, cmul_i(n2));
+        v[1] = cadd(m1, n1); v[4] = csub(m1, n1);
+        v[2] = cadd(m2, n2); v[3] = csub(m2, n2);
     }
 }
 
@@ -128,9 +150,9 @@ template <int M> struct padded_len { static constexpr int value = M + (M >> 4); 
 // One in-place Stockham pass by one warp: reads x[j + q*m] (q < R), writes x[(j-k)*R + k + p*Ls], k = j % Ls.
 // All inputs of the pass sit in registers before the first store, so the pass runs in place; the LAST pass stores to
 // the un-padded (linear) positions, which is what the overlap-add reads with 16-byte loads.
-// tw: this pass's twiddles, compact and conflict-free: tw[(q-1)*Ls + k] = W_{Ls*R}^{q k}.
+// tw: this pass's twiddles, compact and conflict-free: tw[(q-1)*Ls + k] = (w.x, w.y, -w.y, w.x), w = W_{Ls*R}^{q k}.
 template <int M, int R, int LS, bool LAST>
-__device__ __forceinline__ void pass_inplace(float2 * buf, const float2 * tw, int lane) {
+__device__ __forceinline__ void pass_inplace(float2 * buf, const float4 * tw, int lane) {
     constexpr int m = M / R;
     constexpr int B = (m + 31) / 32;
     float2 v[B][R];
@@ -150,7 +172,7 @@ __device__ __forceinline__ void pass_inplace(float2 * buf, const float2 * tw, in
             const int k = j % LS;
             if constexpr (LS > 1) {
 #pragma unroll
-                for (int q = 1; q < R; ++q) v[i][q] = cmul(v[i][q], tw[(q - 1) * LS + k]);
+                for (int q = 1; q < R; ++q) v[i][q] = cmul_pre(v[i][q], tw[(q - 1) * LS + k]);
             }
             dft_any<R>(v[i]);
             const int base = (j - k) * R + k;
@@ -164,9 +186,9 @@ __device__ __forceinline__ void pass_inplace(float2 * buf, const float2 * tw, in
     __syncwarp();
 }
 
-template <int M, int LS> __device__ __forceinline__ void run_passes(float2 *, const float2 *, int) {}
+template <int M, int LS> __device__ __forceinline__ void run_passes(float2 *, const float4 *, int) {}
 template <int M, int LS, int R, int... Rest>
-__device__ __forceinline__ void run_passes(float2 * buf, const float2 * tw, int lane) {
+__device__ __forceinline__ void run_passes(float2 * buf, const float4 * tw, int lane) {
     pass_inplace<M, R, LS, sizeof...(Rest) == 0>(buf, tw, lane);
     run_passes<M, LS * R, Rest...>(buf, tw + (LS > 1 ? (R - 1) * LS : 0), lane);
 }
@@ -176,14 +198,15 @@ template <int M, int LS, int... Rs> struct tw_table_len { static constexpr int v
 template <int M, int LS, int R, int... Rest> struct tw_table_len<M, LS, R, Rest...> {
     static constexpr int value = (LS > 1 ? (R - 1) * LS : 0) + tw_table_len<M, LS * R, Rest...>::value;
 };
-template <int M, int LS> __device__ __forceinline__ void fill_tw(float2 *, const float2 *, int, int) {}
+template <int M, int LS> __device__ __forceinline__ void fill_tw(float4 *, const float2 *, int, int) {}
 template <int M, int LS, int R, int... Rest>
-__device__ __forceinline__ void fill_tw(float2 * dst, const float2 * __restrict__ tw_m, int tid, int nthreads) {
+__device__ __forceinline__ void fill_tw(float4 * dst, const float2 * __restrict__ tw_m, int tid, int nthreads) {
     if constexpr (LS > 1) {
         constexpr int TS = M / (LS * R);
         for (int e = tid; e < (R - 1) * LS; e += nthreads) {
             const int q = e / LS + 1, k = e - (q - 1) * LS;
-            dst[e] = tw_m[q * k * TS];
+            const float2 w = tw_m[q * k * TS];
+            dst[e] = make_float4(w.x, w.y, -w.y, w.x);
         }
     }
     fill_tw<M, LS * R, Rest...>(dst + (LS > 1 ? (R - 1) * LS : 0), tw_m, tid, nthreads);
@@ -197,7 +220,7 @@ __device__ __forceinline__ float2 polar_fast(float logmag, float phase) {
     r = fmaf(-kf, -1.7484555e-7f, r);
     float s, c;
     __sincosf(r, &s, &c);
-    return make_float2(mag * c, mag * s);
+    return mul2(bc(mag), make_float2(c, s));
 }
 
 template <int N, int... RADIX>
@@ -208,13 +231,12 @@ __global__ void __launch_bounds__(FTHREADS, 1) istft_fast_kernel(const fast_para
     static_assert(H % 4 == 0 && MP % 2 == 0, "16-byte rows");
     extern __shared__ __align__(16) uint8_t smem[];
     float2 * s_buf = reinterpret_cast<float2 *>(smem);                  // [FW][MP]
-    float2 * s_tw = s_buf + (size_t) FW * MP;                           // per-pass twiddles
-    float2 * s_twn = s_tw + TWL;                                        // [M/2 + 1]
+    float4 * s_tw = reinterpret_cast<float4 *>(s_buf + (size_t) FW * MP);   // per-pass twiddles (w, i*w)
+    float2 * s_twn = reinterpret_cast<float2 *>(s_tw + TWL);            // [M/2 + 1]
     float * s_hs = reinterpret_cast<float *>(s_twn + (M / 2 + 2));      // [N]  hann * 1/n_freq
-    float * s_env = s_hs + N;                                           // [H]
+    float * s_env = s_hs + N;                                           // [H]  1 / sum of hann^2 over the 4 overlapping frames
     float * s_carry = s_env + H;                                        // [2][CARRY]
     float * s_xm = s_carry + 2 * CARRY;                                 // [FW]
-    int * s_valid = reinterpret_cast<int *>(s_xm + FW);                 // [FW]
 
     const int utt = blockIdx.y;
     const int S = P.n_frames[utt];
@@ -227,14 +249,14 @@ __global__ void __launch_bounds__(FTHREADS, 1) istft_fast_kernel(const fast_para
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     fill_tw<M, 1, RADIX...>(s_tw, P.tw_m, threadIdx.x, FTHREADS);
-    for (int i = threadIdx.x; i <= M / 2; i += FTHREADS) s_twn[i] = P.tw_n[i];
+    for (int i = threadIdx.x; i <= M / 2; i += FTHREADS) { const float2 w = P.tw_n[i]; s_twn[i] = make_float2(0.5f * w.x, 0.5f * w.y); }
     for (int i = threadIdx.x; i < N; i += FTHREADS) s_hs[i] = P.hann[i] * P.scale;
     for (int i = threadIdx.x; i < 2 * CARRY; i += FTHREADS) s_carry[i] = 0.0f;
     for (int r = threadIdx.x; r < H; r += FTHREADS) {   // 4 overlapping frames, ascending frame = descending offset
         float e = 0.0f;
 #pragma unroll
         for (int q = 3; q >= 0; --q) { const float hv = P.hann[r + q * H]; e += hv * hv; }
-        s_env[r] = e;
+        s_env[r] = 1.0f / e;     // steady-state envelope (>= 1.5 for the periodic Hann at 4x overlap): multiply instead of divide
     }
 
     long long lf = a - N >= 0 ? (a - N) / H + 1 : 0;
@@ -243,7 +265,10 @@ __global__ void __launch_bounds__(FTHREADS, 1) istft_fast_kernel(const fast_para
 
     float2 * buf = s_buf + (size_t) warp * MP;
     const float * spec_u = P.spec + (size_t) P.spec_row0[utt] * P.pitch;
-    float * audio_u = P.audio + P.audio_off[utt];
+    // samples [ri_lo, ri_hi) relative to `a` are this CTA's to emit: inside the chunk and inside the cropped output
+    const int ri_lo = (int) (P.pad - a > 0 ? P.pad - a : 0);
+    const int ri_hi = (int) ((b < out_len + P.pad ? b : out_len + P.pad) - a);
+    float * out_base = P.audio + P.audio_off[utt] + (a - P.pad);
     float peak = 0.0f;
     int cur = 0;
     __syncthreads();
@@ -266,57 +291,56 @@ __global__ void __launch_bounds__(FTHREADS, 1) istft_fast_kernel(const fast_para
                         buf[0] = make_float2(Xk.x, Xk.x);
                         s_xm[warp] = X2.x;
                     } else {
-                        const float2 w = s_twn[k];
-                        const float2 Bk = cmul(Xk, w);
-                        const float2 B2 = cmul(X2, make_float2(-w.x, w.y));
-                        const float2 E = make_float2(0.5f * (Xk.x + X2.x), 0.5f * (Xk.y - X2.y));
-                        const float2 O = make_float2(0.5f * (Bk.x + B2.x), 0.5f * (Bk.y - B2.y));
-                        buf[padi(k)] = make_float2(E.x - O.y, E.y + O.x);
-                        if (k2 != k) buf[padi(k2)] = make_float2(E.x + O.y, O.x - E.y);
+                        // E = (X_k + conj X_{M-k}) / 2, O = w_k (X_k - conj X_{M-k}) / 2 (s_twn holds w / 2):
+                        // z_k = E + iO, z_{M-k} = conj(E - iO)
+                        const float2 X2c = make_float2(X2.x, -X2.y);
+                        const float2 iO = cmul_i(cmul(csub(Xk, X2c), s_twn[k]));
+                        const float2 E = mul2(bc(0.5f), cadd(Xk, X2c));
+                        buf[padi(k)] = cadd(E, iO);
+                        if (k2 != k) { const float2 t = csub(E, iO); buf[padi(k2)] = make_float2(t.x, -t.y); }
                     }
                 }
             }
             __syncwarp();
             run_passes<M, 1, RADIX...>(buf, s_tw, lane);
         }
-        if (lane == 0) s_valid[warp] = valid ? 1 : 0;
         __syncthreads();
 
         // ---------------- phase 2: overlap-add the round four samples at a time, emit finished samples ----------------
-        const long long base = lr0 * H;
+        const int n_valid = (int) (ll - lr0 + 1 < FW ? ll - lr0 + 1 : FW);     // frames of this round that exist (a prefix)
+        const int rel0 = (int) (lr0 * H - a);                                    // sample index of the round, relative to a
         const float * carry_in = s_carry + cur * CARRY;
         float * carry_out = s_carry + (cur ^ 1) * CARRY;
         for (int x4 = threadIdx.x; x4 < (SPAN + CARRY) / 4; x4 += FTHREADS) {
             const int x = x4 * 4;
-            const bool to_carry = x >= SPAN;
-            float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-            if (!to_carry && x < CARRY) acc = *reinterpret_cast<const float4 *>(carry_in + x);
-            const int q = x / H;
-            const int w_lo = q - 3 > 0 ? q - 3 : 0;
-            const int w_hi = q < FW - 1 ? q : FW - 1;
-            for (int w = w_lo; w <= w_hi; ++w) {      // ascending frame, like the reference's accumulation order
-                if (s_valid[w] == 0) continue;
-                const int t = x - w * H;
-                const float4 z = *reinterpret_cast<const float4 *>(reinterpret_cast<const float *>(s_buf + (size_t) w * MP) + t);
-                const float4 hs = *reinterpret_cast<const float4 *>(s_hs + t);
-                const float xm = s_xm[w];
-                acc.x = fmaf(z.x + xm, hs.x, acc.x);
-                acc.y = fmaf(z.y - xm, hs.y, acc.y);
-                acc.z = fmaf(z.z + xm, hs.z, acc.z);
-                acc.w = fmaf(z.w - xm, hs.w, acc.w);
+            const int q = x / H, r = x - q * H;
+            float2 a0 = make_float2(0.0f, 0.0f), a1 = a0;
+            if (x < CARRY) { const float4 c = *reinterpret_cast<const float4 *>(carry_in + x); a0 = make_float2(c.x, c.y); a1 = make_float2(c.z, c.w); }
+#pragma unroll
+            for (int d = 3; d >= 0; --d) {            // frame w = q - d: ascending frames, like the reference's accumulation order
+                const int w = q - d;
+                if (w >= 0 && w < n_valid) {
+                    const int t = r + d * H;
+                    const float4 z = *reinterpret_cast<const float4 *>(reinterpret_cast<const float *>(s_buf + (size_t) w * MP) + t);
+                    const float4 hs = *reinterpret_cast<const float4 *>(s_hs + t);
+                    const float xm = s_xm[w];
+                    const float2 nyq = make_float2(xm, -xm);            // the Nyquist bin alternates sign; t is a multiple of 4
+                    a0 = fma2(cadd(make_float2(z.x, z.y), nyq), make_float2(hs.x, hs.y), a0);
+                    a1 = fma2(cadd(make_float2(z.z, z.w), nyq), make_float2(hs.z, hs.w), a1);
+                }
             }
-            if (to_carry) {
-                *reinterpret_cast<float4 *>(carry_out + (x - SPAN)) = acc;
+            if (x >= SPAN) {
+                *reinterpret_cast<float4 *>(carry_out + (x - SPAN)) = make_float4(a0.x, a0.y, a1.x, a1.y);
             } else {
-                const long long i = base + x;
-                const long long o = i - P.pad;
-                if (i >= a && i < b && o >= 0 && o < out_len) {
-                    const int fi = (int) (lr0 + q);           // hop index of these four samples
-                    const int r = x - q * H;
-                    float4 env;
+                const int ri = rel0 + x;
+                if (ri >= ri_lo && ri < ri_hi) {
+                    const int fi = (int) lr0 + q;                         // hop index of these four samples
+                    float4 y;
                     if (fi >= 3 && fi <= S - 1) {
-                        env = *reinterpret_cast<const float4 *>(s_env + r);
-                    } else {
+                        const float4 ie = *reinterpret_cast<const float4 *>(s_env + r);
+                        const float2 y0 = mul2(a0, make_float2(ie.x, ie.y)), y1 = mul2(a1, make_float2(ie.z, ie.w));
+                        y = make_float4(y0.x, y0.y, y1.x, y1.y);
+                    } else {                                              // first / last three hops: partial envelope
                         const int e_lo = fi - 3 > 0 ? fi - 3 : 0;
                         const int e_hi = fi < S - 1 ? fi : S - 1;
                         float e[4] = {0.0f, 0.0f, 0.0f, 0.0f};
@@ -324,17 +348,13 @@ __global__ void __launch_bounds__(FTHREADS, 1) istft_fast_kernel(const fast_para
 #pragma unroll
                             for (int c = 0; c < 4; ++c) { const float hv = P.hann[r + c + (fi - f) * H]; e[c] += hv * hv; }
                         }
-                        env = make_float4(e[0], e[1], e[2], e[3]);
+                        y = make_float4(e[0] > 1e-12f ? a0.x / e[0] : a0.x, e[1] > 1e-12f ? a0.y / e[1] : a0.y,
+                                        e[2] > 1e-12f ? a1.x / e[2] : a1.x, e[3] > 1e-12f ? a1.y / e[3] : a1.y);
                     }
-                    float4 y = acc;
-                    if (env.x > 1e-12f) y.x /= env.x;
-                    if (env.y > 1e-12f) y.y /= env.y;
-                    if (env.z > 1e-12f) y.z /= env.z;
-                    if (env.w > 1e-12f) y.w /= env.w;
-                    *reinterpret_cast<float4 *>(audio_u + o) = y;
+                    *reinterpret_cast<float4 *>(out_base + ri) = y;
                     const float av[4] = {fabsf(y.x), fabsf(y.y), fabsf(y.z), fabsf(y.w)};
 #pragma unroll
-                    for (int c = 0; c < 4; ++c) if (av[c] <= 3.402823466e38f) peak = fmaxf(peak, av[c]);
+                    for (int c = 0; c < 4; ++c) peak = fmaxf(peak, av[c] <= 3.402823466e38f ? av[c] : 0.0f);
                 }
             }
         }
@@ -353,7 +373,7 @@ template <int N, int... RADIX>
 void launch_fast_t(fast_params P, const int * h_frames, int n_utt, int max_frames, cudaStream_t st) {
     constexpr int M = N / 2, H = N / 4, MP = padded_len<M>::value;
     constexpr int TWL = tw_table_len<M, 1, RADIX...>::value;
-    const size_t smem = (size_t) FW * MP * 8 + (size_t) TWL * 8 + (size_t) (M / 2 + 2) * 8 + (size_t) N * 4 + (size_t) H * 4 +
+    const size_t smem = (size_t) FW * MP * 8 + (size_t) TWL * 16 + (size_t) (M / 2 + 2) * 8 + (size_t) N * 4 + (size_t) H * 4 +
                         (size_t) 2 * (N - H) * 4 + FW * 8 + 64;
     static bool configured[64] = {false};
     static int n_sm[64] = {0};
