@@ -50,7 +50,7 @@ void set_err(char * err, size_t err_size, const std::string & msg) {   // lib.cp
 bool env_batching(int out[3]) {
     const char * e = std::getenv("MIO_TTS_B200_BATCHING");
     if (e == nullptr || e[0] == '\0' || (e[0] == '0' && e[1] == '\0')) return false;
-    out[0] = 64; out[1] = 300; out[2] = 2;
+    out[0] = 64; out[1] = 300; out[2] = 4;
     std::sscanf(e, "%d,%d,%d", &out[0], &out[1], &out[2]);
     return out[0] > 0;
 }
@@ -680,7 +680,7 @@ bool mio_tts_b200_context_enable_batching(struct mio_tts_context * ctx, int32_t 
     if (ctx == nullptr || !ctx->mdl) { set_err(err, err_size, "context is null"); return false; }
     if (max_batch <= 0) { ctx->bat.reset(); return true; }
     return guarded(err, err_size, [&] {
-        ctx->bat = std::make_shared<batcher>(ctx->mdl, max_batch, max_wait_us, workers <= 0 ? 2 : workers);
+        ctx->bat = std::make_shared<batcher>(ctx->mdl, max_batch, max_wait_us, workers <= 0 ? 4 : workers);
     });
 }
 
@@ -716,6 +716,7 @@ bool mio_tts_reserve_workspace(struct mio_tts_context * ctx, int32_t n_codes, ch
     if (!guarded(err, err_size, [&] {
             std::lock_guard<std::mutex> lk(ctx->eng->mtx);
             ctx->eng->reserve(n, 1);
+            if (ctx->bat) ctx->bat->reserve(n);   // batching on: every worker engine, for max_batch such utterances
         })) {
         set_err(err, err_size, "failed to reserve decode workspace");
         return false;

@@ -3,6 +3,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <functional>
 #include <cstring>
 
 namespace mio {
@@ -15,7 +16,7 @@ void wav16_header(uint8_t * p, uint32_t sample_rate, uint32_t pcm_bytes) {
     std::memcpy(p + 36, "data", 4); u32(40, pcm_bytes);
 }
 
-void decode_batch(engine & E, decode_request * const * reqs, size_t batch) {
+void decode_batch(engine & E, decode_request * const * reqs, size_t batch, const std::function<void()> & kernels_done) {
     std::vector<const int32_t *> codes(batch);
     std::vector<size_t> n(batch);
     std::vector<const float *> embs(batch);
@@ -28,6 +29,10 @@ void decode_batch(engine & E, decode_request * const * reqs, size_t batch) {
         E.out_pcm16 = wav16;
         E.prepare(codes.data(), n.data(), has_emb ? embs.data() : nullptr, has_emb ? reqs[0]->n_emb : 0, batch);
         E.run(true);
+        if (kernels_done) {          // the batcher hands the GPU to its other worker here: our D2H runs under its kernels
+            E.sync();
+            kernels_done();
+        }
         for (size_t u = 0; u < batch; ++u) {
             const size_t ns = E.audio_len(u);
             bufs[u] = wav16 ? (void *) result_alloc((44 + 2 * ns + 3) / 4) : (void *) result_alloc(ns);
@@ -44,6 +49,7 @@ void decode_batch(engine & E, decode_request * const * reqs, size_t batch) {
     } catch (...) {
         E.out_pcm16 = false;
         try { E.sync(); } catch (...) {}
+        if (kernels_done) kernels_done();
         for (void * p : bufs) if (p && !result_free(p)) std::free(p);
         throw;
     }
@@ -66,6 +72,13 @@ batcher::~batcher() {
     for (auto & t : th_) t.join();
 }
 
+void batcher::reserve(int n_codes) {
+    for (auto & e : eng_) {
+        std::lock_guard<std::mutex> lk(e->mtx);
+        e->reserve(n_codes, max_batch);
+    }
+}
+
 batcher_stats batcher::stats() {
     std::lock_guard<std::mutex> lk(m_);
     return st_;
@@ -75,7 +88,7 @@ void batcher::submit(decode_request & r) {
     std::unique_lock<std::mutex> lk(m_);
     if (stop_) { r.err = "batcher is shutting down"; r.done = true; return; }
     q_.push_back(&r);
-    cv_work_.notify_one();
+    cv_work_.notify_all();
     cv_done_.wait(lk, [&] { return r.done; });
 }
 
@@ -84,19 +97,23 @@ void batcher::loop(int w) {
     std::vector<decode_request *> take;
     for (;;) {
         take.clear();
+        size_t codes = 0;
         {
+            // Admission: a worker starts a batch only while the kernels already running cover fewer than sat_codes_ codes.
+            // Small batches are launch-latency bound and overlap well on the GPU, so they run side by side (never slower
+            // than plain clones); once the GPU is saturated, requests pile up in the queue and the next admitted worker
+            // takes all of them -- the batch size follows the load with no timer involved.
             std::unique_lock<std::mutex> lk(m_);
-            cv_work_.wait(lk, [&] { return stop_ || !q_.empty(); });
-            if (q_.empty()) return;   // stop_ and drained
-            // Gathering window: callers released by the previous batch come back within microseconds of each other;
-            // wait (bounded) until as many as last time are queued instead of peeling the first one off alone.
+            cv_work_.wait(lk, [&] { return stop_ || (!q_.empty() && busy_codes_ < sat_codes_); });
+            if (q_.empty()) { if (stop_) return; continue; }
+            // Callers released together by a finished batch come back within microseconds of each other: give them a
+            // bounded moment so the first one back is not peeled off alone.
             const size_t want = std::min<size_t>((size_t) max_batch, std::max<size_t>(expect_, 1));
-            if (max_wait_us > 0 && q_.size() < want)
+            if (max_wait_us > 0 && q_.size() < want && !stop_)
                 cv_work_.wait_for(lk, std::chrono::microseconds(max_wait_us), [&] { return stop_ || q_.size() >= want; });
-            if (q_.empty()) continue;   // another worker took them during the window
+            if (q_.empty()) continue;      // another worker took them during the window
             decode_request * head = q_.front();
             const bool he = head->emb != nullptr && head->n_emb > 0;
-            size_t codes = 0;
             for (auto it = q_.begin(); it != q_.end() && take.size() < (size_t) max_batch;) {
                 decode_request * r = *it;
                 const bool re = r->emb != nullptr && r->n_emb > 0;
@@ -112,12 +129,19 @@ void batcher::loop(int w) {
             st_.requests += take.size();
             st_.batches += 1;
             st_.largest = std::max<uint64_t>(st_.largest, take.size());
-            expect_ = take.size();
-            if (!q_.empty()) cv_work_.notify_one();   // incompatible or overflow requests: next worker
+            busy_codes_ += codes;
+            expect_ = 1;                   // until a batch finishes and tells how many callers are on their way back
         }
+        bool released = false;
+        auto release = [&] {               // kernels done: admit the next batch; our D2H copies run under its kernels
+            if (released) return;
+            released = true;
+            { std::lock_guard<std::mutex> lk(m_); busy_codes_ -= codes; }
+            cv_work_.notify_all();
+        };
         bool whole = true;
         try {
-            decode_batch(E, take.data(), take.size());
+            decode_batch(E, take.data(), take.size(), release);
         } catch (const std::exception & e) {
             whole = false;
             if (take.size() == 1) take[0]->err = e.what();
@@ -125,6 +149,7 @@ void batcher::loop(int w) {
             whole = false;
             if (take.size() == 1) take[0]->err = "unknown error";
         }
+        release();
         if (!whole && take.size() > 1) {
             // one bad request (e.g. an out-of-range code) must not fail its neighbours: decode each on its own so
             // every caller gets exactly the error (or the audio) an un-batched call would have given
@@ -143,6 +168,7 @@ void batcher::loop(int w) {
         {
             std::lock_guard<std::mutex> lk(m_);
             for (decode_request * r : take) r->done = true;
+            expect_ = take.size();
         }
         cv_done_.notify_all();
     }

@@ -150,9 +150,13 @@ template <int M> struct padded_len { static constexpr int value = M + (M >> 4); 
 // One in-place Stockham pass by one warp: reads x[j + q*m] (q < R), writes x[(j-k)*R + k + p*Ls], k = j % Ls.
 // All inputs of the pass sit in registers before the first store, so the pass runs in place; the LAST pass stores to
 // the un-padded (linear) positions, which is what the overlap-add reads with 16-byte loads.
-// tw: this pass's twiddles, compact and conflict-free: tw[(q-1)*Ls + k] = (w.x, w.y, -w.y, w.x), w = W_{Ls*R}^{q k}.
+// tw: this pass's twiddles w = W_{Ls*R}^{q k}, compact and conflict-free at [(q-1)*Ls + k].  When Ls divides 32 every
+// butterfly of a lane has the same k, so the R-1 twiddles are loaded once per frame and shared by the lane's butterflies.
+template <int LS> struct tw_shared { static constexpr bool value = LS > 1 && (32 % LS) == 0; };
+template <int R, int LS> struct tw_units { static constexpr int value = LS > 1 ? (R - 1) * LS : 0; };
+
 template <int M, int R, int LS, bool LAST>
-__device__ __forceinline__ void pass_inplace(float2 * buf, const float4 * tw, int lane) {
+__device__ __forceinline__ void pass_inplace(float2 * buf, const float2 * tw, int lane) {
     constexpr int m = M / R;
     constexpr int B = (m + 31) / 32;
     float2 v[B][R];
@@ -164,15 +168,23 @@ __device__ __forceinline__ void pass_inplace(float2 * buf, const float4 * tw, in
             for (int q = 0; q < R; ++q) v[i][q] = buf[padi(j + q * m)];
         }
     }
+    float2 ws[tw_shared<LS>::value ? R : 1];
+    if constexpr (tw_shared<LS>::value) {
+#pragma unroll
+        for (int q = 1; q < R; ++q) ws[q] = tw[(q - 1) * LS + lane % LS];
+    }
     __syncwarp();
 #pragma unroll
     for (int i = 0; i < B; ++i) {
         const int j = lane + 32 * i;
         if (j < m) {
             const int k = j % LS;
-            if constexpr (LS > 1) {
+            if constexpr (tw_shared<LS>::value) {
 #pragma unroll
-                for (int q = 1; q < R; ++q) v[i][q] = cmul_pre(v[i][q], tw[(q - 1) * LS + k]);
+                for (int q = 1; q < R; ++q) v[i][q] = cmul(v[i][q], ws[q]);
+            } else if constexpr (LS > 1) {
+#pragma unroll
+                for (int q = 1; q < R; ++q) v[i][q] = cmul(v[i][q], tw[(q - 1) * LS + k]);
             }
             dft_any<R>(v[i]);
             const int base = (j - k) * R + k;
@@ -186,30 +198,30 @@ __device__ __forceinline__ void pass_inplace(float2 * buf, const float4 * tw, in
     __syncwarp();
 }
 
-template <int M, int LS> __device__ __forceinline__ void run_passes(float2 *, const float4 *, int) {}
+template <int M, int LS> __device__ __forceinline__ void run_passes(float2 *, const float2 *, int) {}
 template <int M, int LS, int R, int... Rest>
-__device__ __forceinline__ void run_passes(float2 * buf, const float4 * tw, int lane) {
+__device__ __forceinline__ void run_passes(float2 * buf, const float2 * tw, int lane) {
     pass_inplace<M, R, LS, sizeof...(Rest) == 0>(buf, tw, lane);
-    run_passes<M, LS * R, Rest...>(buf, tw + (LS > 1 ? (R - 1) * LS : 0), lane);
+    run_passes<M, LS * R, Rest...>(buf, tw + tw_units<R, LS>::value, lane);
 }
 
-// per-pass twiddle tables, laid out in pass order (the first pass has none)
+// per-pass twiddle tables in float2 units, laid out in pass order (the first pass has none)
 template <int M, int LS, int... Rs> struct tw_table_len { static constexpr int value = 0; };
 template <int M, int LS, int R, int... Rest> struct tw_table_len<M, LS, R, Rest...> {
-    static constexpr int value = (LS > 1 ? (R - 1) * LS : 0) + tw_table_len<M, LS * R, Rest...>::value;
+    static constexpr int value = tw_units<R, LS>::value + tw_table_len<M, LS * R, Rest...>::value;
 };
-template <int M, int LS> __device__ __forceinline__ void fill_tw(float4 *, const float2 *, int, int) {}
+template <int M, int LS> __device__ __forceinline__ void fill_tw(float2 *, const float2 *, int, int) {}
 template <int M, int LS, int R, int... Rest>
-__device__ __forceinline__ void fill_tw(float4 * dst, const float2 * __restrict__ tw_m, int tid, int nthreads) {
+__device__ __forceinline__ void fill_tw(float2 * dst, const float2 * __restrict__ tw_m, int tid, int nthreads) {
     if constexpr (LS > 1) {
         constexpr int TS = M / (LS * R);
         for (int e = tid; e < (R - 1) * LS; e += nthreads) {
             const int q = e / LS + 1, k = e - (q - 1) * LS;
             const float2 w = tw_m[q * k * TS];
-            dst[e] = make_float4(w.x, w.y, -w.y, w.x);
+            dst[e] = w;
         }
     }
-    fill_tw<M, LS * R, Rest...>(dst + (LS > 1 ? (R - 1) * LS : 0), tw_m, tid, nthreads);
+    fill_tw<M, LS * R, Rest...>(dst + tw_units<R, LS>::value, tw_m, tid, nthreads);
 }
 
 // X_k = min(exp(logmag), 100) * (cos phi, sin phi) on the SFU
@@ -228,11 +240,11 @@ __global__ void __launch_bounds__(FTHREADS, 1) istft_fast_kernel(const fast_para
     MIO_PDL_PROLOGUE();
     constexpr int M = N / 2, H = N / 4, CARRY = N - H, SPAN = FW * H, MP = padded_len<M>::value;
     constexpr int TWL = tw_table_len<M, 1, RADIX...>::value;
-    static_assert(H % 4 == 0 && MP % 2 == 0, "16-byte rows");
+    static_assert(H % 4 == 0 && MP % 2 == 0 && TWL % 2 == 0, "16-byte rows");
     extern __shared__ __align__(16) uint8_t smem[];
     float2 * s_buf = reinterpret_cast<float2 *>(smem);                  // [FW][MP]
-    float4 * s_tw = reinterpret_cast<float4 *>(s_buf + (size_t) FW * MP);   // per-pass twiddles (w, i*w)
-    float2 * s_twn = reinterpret_cast<float2 *>(s_tw + TWL);            // [M/2 + 1]
+    float2 * s_tw = s_buf + (size_t) FW * MP;                           // per-pass twiddles (TWL float2 units, even)
+    float2 * s_twn = s_tw + TWL;                                        // [M/2 + 1]
     float * s_hs = reinterpret_cast<float *>(s_twn + (M / 2 + 2));      // [N]  hann * 1/n_freq
     float * s_env = s_hs + N;                                           // [H]  1 / sum of hann^2 over the 4 overlapping frames
     float * s_carry = s_env + H;                                        // [2][CARRY]
@@ -279,8 +291,16 @@ __global__ void __launch_bounds__(FTHREADS, 1) istft_fast_kernel(const fast_para
         const bool valid = l <= ll;
         if (valid) {
             const float * fr = spec_u + (size_t) l * P.pitch;
+            // The CTA's warps move through the phases together, so the memory system would idle during the FFT and
+            // the overlap-add: pull the NEXT round's spectrum row into L2 now (one 128-byte line per lane, twice).
+            if (l + FW <= ll) {
+                const char * nx = reinterpret_cast<const char *>(fr + (size_t) FW * P.pitch);
+#pragma unroll
+                for (int c = 0; c < (N + 2) * 4; c += 32 * 128)
+                    if (c + lane * 128 < (N + 2) * 4) asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + c + lane * 128));
+            }
             constexpr int ITER = (M / 2) / 32 + 1;
-#pragma unroll 4
+#pragma unroll 8
             for (int i = 0; i < ITER; ++i) {
                 const int k = lane + 32 * i;
                 if (k <= M / 2) {
@@ -311,51 +331,56 @@ __global__ void __launch_bounds__(FTHREADS, 1) istft_fast_kernel(const fast_para
         const int rel0 = (int) (lr0 * H - a);                                    // sample index of the round, relative to a
         const float * carry_in = s_carry + cur * CARRY;
         float * carry_out = s_carry + (cur ^ 1) * CARRY;
-        for (int x4 = threadIdx.x; x4 < (SPAN + CARRY) / 4; x4 += FTHREADS) {
-            const int x = x4 * 4;
-            const int q = x / H, r = x - q * H;
-            float2 a0 = make_float2(0.0f, 0.0f), a1 = a0;
-            if (x < CARRY) { const float4 c = *reinterpret_cast<const float4 *>(carry_in + x); a0 = make_float2(c.x, c.y); a1 = make_float2(c.z, c.w); }
+        // A thread keeps one 4-sample column r of the hop and walks the hops q = grp, grp + GROUPS, ...: its window
+        // values hs[r + d*H] and its envelope are the same for every hop, so they are loaded once per round.
+        constexpr int H4 = H / 4, GROUPS = FTHREADS / H4;
+        const int grp = threadIdx.x / H4, r = (threadIdx.x - grp * H4) * 4;
+        if (grp < GROUPS) {
+            float4 hsd[4];
 #pragma unroll
-            for (int d = 3; d >= 0; --d) {            // frame w = q - d: ascending frames, like the reference's accumulation order
-                const int w = q - d;
-                if (w >= 0 && w < n_valid) {
-                    const int t = r + d * H;
-                    const float4 z = *reinterpret_cast<const float4 *>(reinterpret_cast<const float *>(s_buf + (size_t) w * MP) + t);
-                    const float4 hs = *reinterpret_cast<const float4 *>(s_hs + t);
-                    const float xm = s_xm[w];
-                    const float2 nyq = make_float2(xm, -xm);            // the Nyquist bin alternates sign; t is a multiple of 4
-                    a0 = fma2(cadd(make_float2(z.x, z.y), nyq), make_float2(hs.x, hs.y), a0);
-                    a1 = fma2(cadd(make_float2(z.z, z.w), nyq), make_float2(hs.z, hs.w), a1);
-                }
-            }
-            if (x >= SPAN) {
-                *reinterpret_cast<float4 *>(carry_out + (x - SPAN)) = make_float4(a0.x, a0.y, a1.x, a1.y);
-            } else {
-                const int ri = rel0 + x;
-                if (ri >= ri_lo && ri < ri_hi) {
-                    const int fi = (int) lr0 + q;                         // hop index of these four samples
-                    float4 y;
-                    if (fi >= 3 && fi <= S - 1) {
-                        const float4 ie = *reinterpret_cast<const float4 *>(s_env + r);
-                        const float2 y0 = mul2(a0, make_float2(ie.x, ie.y)), y1 = mul2(a1, make_float2(ie.z, ie.w));
-                        y = make_float4(y0.x, y0.y, y1.x, y1.y);
-                    } else {                                              // first / last three hops: partial envelope
-                        const int e_lo = fi - 3 > 0 ? fi - 3 : 0;
-                        const int e_hi = fi < S - 1 ? fi : S - 1;
-                        float e[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-                        for (int f = e_lo; f <= e_hi; ++f) {
+            for (int d = 0; d < 4; ++d) hsd[d] = *reinterpret_cast<const float4 *>(s_hs + r + d * H);
+            const float4 ie = *reinterpret_cast<const float4 *>(s_env + r);
+            for (int q = grp; q < FW + 3; q += GROUPS) {         // hops FW .. FW+2 are the carry into the next round
+                const int x = q * H + r;
+                float2 a0 = make_float2(0.0f, 0.0f), a1 = a0;
+                if (q < 3) { const float4 c = *reinterpret_cast<const float4 *>(carry_in + x); a0 = make_float2(c.x, c.y); a1 = make_float2(c.z, c.w); }
 #pragma unroll
-                            for (int c = 0; c < 4; ++c) { const float hv = P.hann[r + c + (fi - f) * H]; e[c] += hv * hv; }
-                        }
-                        y = make_float4(e[0] > 1e-12f ? a0.x / e[0] : a0.x, e[1] > 1e-12f ? a0.y / e[1] : a0.y,
-                                        e[2] > 1e-12f ? a1.x / e[2] : a1.x, e[3] > 1e-12f ? a1.y / e[3] : a1.y);
+                for (int d = 3; d >= 0; --d) {        // frame w = q - d: ascending frames, like the reference's accumulation order
+                    const int w = q - d;
+                    if (w >= 0 && w < n_valid) {
+                        const float4 z = *reinterpret_cast<const float4 *>(reinterpret_cast<const float *>(s_buf + (size_t) w * MP) + r + d * H);
+                        const float xm = s_xm[w];
+                        const float2 nyq = make_float2(xm, -xm);        // the Nyquist bin alternates sign; r + d*H is a multiple of 4
+                        a0 = fma2(cadd(make_float2(z.x, z.y), nyq), make_float2(hsd[d].x, hsd[d].y), a0);
+                        a1 = fma2(cadd(make_float2(z.z, z.w), nyq), make_float2(hsd[d].z, hsd[d].w), a1);
                     }
-                    *reinterpret_cast<float4 *>(out_base + ri) = y;
-                    const float av[4] = {fabsf(y.x), fabsf(y.y), fabsf(y.z), fabsf(y.w)};
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) peak = fmaxf(peak, av[c] <= 3.402823466e38f ? av[c] : 0.0f);
                 }
+                if (q >= FW) {
+                    *reinterpret_cast<float4 *>(carry_out + (x - SPAN)) = make_float4(a0.x, a0.y, a1.x, a1.y);
+                    continue;
+                }
+                const int ri = rel0 + x;
+                if (ri < ri_lo || ri >= ri_hi) continue;
+                const int fi = (int) lr0 + q;                             // hop index of these four samples
+                float4 y;
+                if (fi >= 3 && fi <= S - 1) {
+                    const float2 y0 = mul2(a0, make_float2(ie.x, ie.y)), y1 = mul2(a1, make_float2(ie.z, ie.w));
+                    y = make_float4(y0.x, y0.y, y1.x, y1.y);
+                } else {                                                  // first / last three hops: partial envelope
+                    const int e_lo = fi - 3 > 0 ? fi - 3 : 0;
+                    const int e_hi = fi < S - 1 ? fi : S - 1;
+                    float e[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+                    for (int f = e_lo; f <= e_hi; ++f) {
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) { const float hv = P.hann[r + c + (fi - f) * H]; e[c] += hv * hv; }
+                    }
+                    y = make_float4(e[0] > 1e-12f ? a0.x / e[0] : a0.x, e[1] > 1e-12f ? a0.y / e[1] : a0.y,
+                                    e[2] > 1e-12f ? a1.x / e[2] : a1.x, e[3] > 1e-12f ? a1.y / e[3] : a1.y);
+                }
+                *reinterpret_cast<float4 *>(out_base + ri) = y;
+                const float av[4] = {fabsf(y.x), fabsf(y.y), fabsf(y.z), fabsf(y.w)};
+#pragma unroll
+                for (int c = 0; c < 4; ++c) peak = fmaxf(peak, av[c] <= 3.402823466e38f ? av[c] : 0.0f);
             }
         }
         cur ^= 1;
@@ -373,7 +398,7 @@ template <int N, int... RADIX>
 void launch_fast_t(fast_params P, const int * h_frames, int n_utt, int max_frames, cudaStream_t st) {
     constexpr int M = N / 2, H = N / 4, MP = padded_len<M>::value;
     constexpr int TWL = tw_table_len<M, 1, RADIX...>::value;
-    const size_t smem = (size_t) FW * MP * 8 + (size_t) TWL * 16 + (size_t) (M / 2 + 2) * 8 + (size_t) N * 4 + (size_t) H * 4 +
+    const size_t smem = (size_t) FW * MP * 8 + (size_t) TWL * 8 + (size_t) (M / 2 + 2) * 8 + (size_t) N * 4 + (size_t) H * 4 +
                         (size_t) 2 * (N - H) * 4 + FW * 8 + 64;
     static bool configured[64] = {false};
     static int n_sm[64] = {0};
