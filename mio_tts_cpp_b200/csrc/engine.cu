@@ -54,9 +54,20 @@ float * result_alloc(size_t n_floats) {
             return (float *) p;
         }
     }
+    // Grow by slabs: cudaHostAlloc takes driver-wide locks (it stalls the launches of every other slot), so one call
+    // brings in 32 MB worth of buffers of this class instead of one buffer.
+    const size_t n_buf = std::max<size_t>(1, (32u << 20) / cls);
     void * p = nullptr;
-    if (cudaHostAlloc(&p, cls, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (cudaHostAlloc(&p, cls * n_buf, cudaHostAllocPortable) != cudaSuccess) {
+        cudaGetLastError();
+        if (n_buf == 1 || cudaHostAlloc(&p, cls, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        std::lock_guard<std::mutex> lk(P.mtx);
+        P.live[p] = cls;
+        return (float *) p;
+    }
     std::lock_guard<std::mutex> lk(P.mtx);
+    auto & fl = P.free_list[cls];
+    for (size_t i = 1; i < n_buf; ++i) fl.push_back((uint8_t *) p + i * cls);
     P.live[p] = cls;
     return (float *) p;
 }

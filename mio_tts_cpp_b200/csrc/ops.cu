@@ -92,57 +92,79 @@ __global__ void __launch_bounds__(256) cond_kernel(const float * __restrict__ w,
 // ---- LayerNorm (ggml_norm, biased variance, ggml-cpu/ops.cpp:3642-3687) + affine (layer_norm(),
 //      src/miocodec-decoder.cpp:136-150) or AdaLN xn*(1+scale)+shift (adaln_apply :1183-1188).
 //      One warp per row, row kept in registers (dim = 128*NV), fp32 statistics, 16-bit or fp32 output. ----
-template <int NV>
-__global__ void layernorm_kernel(const float * __restrict__ x, int rows, float eps, const float * __restrict__ w,
-                                 const float * __restrict__ b, const float * __restrict__ cond, int cond_ld,
-                                 int shift_off, int scale_off, const int * __restrict__ row_utt, void * out16,
-                                 int out_dtype, float * out32) {
+template <int NV, int RW>
+__global__ void __launch_bounds__(256) layernorm_kernel(const float * __restrict__ x, int rows, float eps, const float * __restrict__ w,
+                                                        const float * __restrict__ b, const float * __restrict__ cond, int cond_ld,
+                                                        int shift_off, int scale_off, const int * __restrict__ row_utt, void * out16,
+                                                        int out_dtype, float * out32) {
     MIO_PDL_PROLOGUE();
     constexpr int DIM = NV * 128;
-    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (row >= rows) return;
+    // RW rows per warp, all their loads in flight together; the affine / AdaLN parameters of the first row's utterance
+    // are fetched before the reductions (the other rows almost always share them) so nothing waits on them afterwards
+    const int row0 = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * RW;
+    if (row0 >= rows) return;
     const int lane = threadIdx.x & 31;
-    const int utt = row_utt ? row_utt[row] : 0;
-    const float4 * xr = reinterpret_cast<const float4 *>(x + (size_t) row * DIM);
-    float4 v[NV];
-    float s = 0.0f;
+    float4 v[RW][NV];
+    int utt[RW];
 #pragma unroll
-    for (int i = 0; i < NV; ++i) {
-        v[i] = xr[lane + 32 * i];
-        s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+    for (int r = 0; r < RW; ++r) {
+        const int row = min(row0 + r, rows - 1);
+        utt[r] = row_utt ? row_utt[row] : 0;
+        const float4 * xr = reinterpret_cast<const float4 *>(x + (size_t) row * DIM);
+#pragma unroll
+        for (int i = 0; i < NV; ++i) v[r][i] = xr[lane + 32 * i];
     }
-    const float mean = warp_sum(s) * (1.0f / DIM);
-    float q = 0.0f;
+    float4 pa[NV], pb[NV];      // (scale, shift) or (weight, bias)
+    auto load_params = [&](int u) {
+        const float4 * a4 = cond ? reinterpret_cast<const float4 *>(cond + (size_t) max(u, 0) * cond_ld + scale_off)
+                                 : reinterpret_cast<const float4 *>(w);
+        const float4 * b4 = cond ? reinterpret_cast<const float4 *>(cond + (size_t) max(u, 0) * cond_ld + shift_off)
+                                 : reinterpret_cast<const float4 *>(b);
 #pragma unroll
-    for (int i = 0; i < NV; ++i) {
-        v[i].x -= mean; v[i].y -= mean; v[i].z -= mean; v[i].w -= mean;
-        q += (v[i].x * v[i].x + v[i].y * v[i].y) + (v[i].z * v[i].z + v[i].w * v[i].w);
-    }
-    const float var = warp_sum(q) * (1.0f / DIM);
-    const float rstd = 1.0f / sqrtf(var + eps);
-    const float * shift = cond ? cond + (size_t) max(utt, 0) * cond_ld + shift_off : nullptr;
-    const float * scale = cond ? cond + (size_t) max(utt, 0) * cond_ld + scale_off : nullptr;
+        for (int i = 0; i < NV; ++i) { pa[i] = __ldg(a4 + lane + 32 * i); pb[i] = __ldg(b4 + lane + 32 * i); }
+    };
+    const bool affine = cond != nullptr || w != nullptr;
+    if (affine) load_params(utt[0]);
+    float rstd[RW];
 #pragma unroll
-    for (int i = 0; i < NV; ++i) {
-        const int c4 = lane + 32 * i;
-        float4 y = make_float4(v[i].x * rstd, v[i].y * rstd, v[i].z * rstd, v[i].w * rstd);
-        if (cond) {
-            const float4 sc = __ldg(reinterpret_cast<const float4 *>(scale) + c4);
-            const float4 sh = __ldg(reinterpret_cast<const float4 *>(shift) + c4);
-            y.x = y.x * (sc.x + 1.0f) + sh.x; y.y = y.y * (sc.y + 1.0f) + sh.y;
-            y.z = y.z * (sc.z + 1.0f) + sh.z; y.w = y.w * (sc.w + 1.0f) + sh.w;
-        } else if (w) {
-            const float4 ww = __ldg(reinterpret_cast<const float4 *>(w) + c4);
-            const float4 bb = __ldg(reinterpret_cast<const float4 *>(b) + c4);
-            y.x = y.x * ww.x + bb.x; y.y = y.y * ww.y + bb.y; y.z = y.z * ww.z + bb.z; y.w = y.w * ww.w + bb.w;
+    for (int r = 0; r < RW; ++r) {
+        float s = 0.0f;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) s += (v[r][i].x + v[r][i].y) + (v[r][i].z + v[r][i].w);
+        const float mean = warp_sum(s) * (1.0f / DIM);
+        float q = 0.0f;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            v[r][i].x -= mean; v[r][i].y -= mean; v[r][i].z -= mean; v[r][i].w -= mean;
+            q += (v[r][i].x * v[r][i].x + v[r][i].y * v[r][i].y) + (v[r][i].z * v[r][i].z + v[r][i].w * v[r][i].w);
         }
-        if (utt < 0) y = make_float4(0.f, 0.f, 0.f, 0.f);   // gap row of the layout
-        if (out32) reinterpret_cast<float4 *>(out32 + (size_t) row * DIM)[c4] = y;
-        if (out16) {
-            uint2 o;
-            o.x = pack16(y.x, y.y, out_dtype);
-            o.y = pack16(y.z, y.w, out_dtype);
-            reinterpret_cast<uint2 *>((uint16_t *) out16 + (size_t) row * DIM)[c4] = o;
+        const float var = warp_sum(q) * (1.0f / DIM);
+        rstd[r] = 1.0f / sqrtf(var + eps);
+    }
+#pragma unroll
+    for (int r = 0; r < RW; ++r) {
+        const int row = row0 + r;
+        if (row >= rows) break;
+        if (r > 0 && cond && utt[r] != utt[r - 1]) load_params(utt[r]);
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int c4 = lane + 32 * i;
+            float4 y = make_float4(v[r][i].x * rstd[r], v[r][i].y * rstd[r], v[r][i].z * rstd[r], v[r][i].w * rstd[r]);
+            if (cond) {
+                y.x = y.x * (pa[i].x + 1.0f) + pb[i].x; y.y = y.y * (pa[i].y + 1.0f) + pb[i].y;
+                y.z = y.z * (pa[i].z + 1.0f) + pb[i].z; y.w = y.w * (pa[i].w + 1.0f) + pb[i].w;
+            } else if (w) {
+                y.x = y.x * pa[i].x + pb[i].x; y.y = y.y * pa[i].y + pb[i].y;
+                y.z = y.z * pa[i].z + pb[i].z; y.w = y.w * pa[i].w + pb[i].w;
+            }
+            if (utt[r] < 0) y = make_float4(0.f, 0.f, 0.f, 0.f);   // gap row of the layout
+            if (out32) reinterpret_cast<float4 *>(out32 + (size_t) row * DIM)[c4] = y;
+            if (out16) {
+                uint2 o;
+                o.x = pack16(y.x, y.y, out_dtype);
+                o.y = pack16(y.z, y.w, out_dtype);
+                reinterpret_cast<uint2 *>((uint16_t *) out16 + (size_t) row * DIM)[c4] = o;
+            }
         }
     }
 }
@@ -443,9 +465,10 @@ void launch_layernorm(const float * x, int rows, int dim, float eps, const float
                       void * out16, int out_dtype, float * out32, cudaStream_t st) {
     if (rows <= 0) return;
     const unsigned grid = blocks_for((size_t) rows, 8);
+    const unsigned grid2 = blocks_for((size_t) rows, 16);      // two rows per warp
 #define LN_CASE(NV)                                                                                              \
     case NV:                                                                                                     \
-        launch_pdl(layernorm_kernel<NV>, dim3(grid), dim3(256), 0, st, x, rows, eps, w, b, cond, cond_ld, shift_off, scale_off,      \
+        launch_pdl(layernorm_kernel<NV, 2>, dim3(grid2), dim3(256), 0, st, x, rows, eps, w, b, cond, cond_ld, shift_off, scale_off,  \
                                                    row_utt, out16, out_dtype, out32);                            \
         break;
     if ((dim % 128) == 0 && dim <= 1024 && (!cond || ((cond_ld | shift_off | scale_off) & 3) == 0)) {
