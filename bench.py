@@ -225,6 +225,7 @@ def run_b200(args, rank, world, local_rank):
                             "kernel": "gemm_tcgen05_kernel", "launches_per_step": p["gemm_launches"],
                             "avg_launch_ms": g_ms / max(1, p["gemm_launches"]),
                             "flops_per_launch_avg": p["gemm_flops"] / max(1, p["gemm_launches"]),
+                            "algorithmic_bytes_per_launch_avg": p["gemm_bytes"] / max(1, p["gemm_launches"]),
                             "gemm_share_of_step": g_ms / p["total_ms"],
                             "whole_path_frac": (U.FLOP_PER_TOKEN * BATCH * N_CODES / (ms * 1e-3) / 1e12)
                             / peaks["bf16_tflops_sustained"] if world == 1 else None}

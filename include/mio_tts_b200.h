@@ -210,6 +210,7 @@ struct mio_tts_b200_profile {
     float prenet_ms, upsample_prior_ms, decoder_ms, post_head_ms, istft_ms, total_ms;
     double gemm_ms, gemm_flops; int32_t gemm_launches;
     double attn_ms; int32_t attn_launches;
+    double gemm_bytes;      /* algorithmic DRAM bytes of the GEMM launches: A + W + output + residual */
 };
 MIO_B200_API bool mio_tts_b200_prepare(struct mio_tts_context * ctx, const int32_t * const * codes,
                                        const size_t * n_codes, const float * const * embedding, size_t n_embedding,

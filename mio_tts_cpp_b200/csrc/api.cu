@@ -966,6 +966,7 @@ bool mio_tts_b200_profile_resident(struct mio_tts_context * ctx, struct mio_tts_
         out->post_head_ms = t.post_head; out->istft_ms = t.istft; out->total_ms = t.total;
         out->gemm_ms = t.gemm_ms; out->gemm_flops = t.gemm_flops; out->gemm_launches = t.gemm_launches;
         out->attn_ms = t.attn_ms; out->attn_launches = t.attn_launches;
+        out->gemm_bytes = t.gemm_bytes;
     });
 }
 

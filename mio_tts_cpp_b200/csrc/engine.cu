@@ -418,6 +418,10 @@ void engine::gemm(const dbuf & a, const dev_linear & w, int M, int epilogue, voi
     if (prof_gemm_) {
         MIO_CUDA(cudaEventRecord(gemm_ev_[evi + 1], st_));
         gemm_ev_flops_.push_back({evi, 2.0 * (double) (lay ? lay->valid : M) * w.N * w.K * w.taps});
+        // algorithmic DRAM bytes of this launch: A once (the taps re-read the same rows), W once, the output, the residual
+        const double out_cols = epilogue == EPI_SWIGLU16 ? w.N / 2 : w.N;
+        gemm_bytes_ += (double) M * w.K * 2 + (double) w.N * w.K * w.taps * 2 + (double) M * out_cols * (epilogue == EPI_STORE32 ? 4 : 2) +
+                       (res ? (double) M * w.N * 4 : 0.0);
         gemm_ev_shape_.push_back({M, w.N, w.K, w.taps, epilogue});
     }
 }
@@ -479,6 +483,7 @@ void engine::run(bool with_istft, stage_times * prof, int stop_stage) {
     prof_ = prof;
     prof_gemm_ = prof != nullptr;
     gemm_ev_flops_.clear();
+    gemm_bytes_ = 0;
     gemm_ev_shape_.clear();
     attn_ev_.clear();
     const int pd = hp.prenet_dim, dd = hp.decoder_dim;
@@ -582,7 +587,7 @@ void engine::run(bool with_istft, stage_times * prof, int stop_stage) {
         auto ms = [&](int a, int b) { float t = 0; cudaEventElapsedTime(&t, ev_[a], ev_[b]); return t; };
         prof->prenet = ms(0, 1); prof->upsample_prior = ms(1, 2); prof->decoder = ms(2, 3);
         prof->post_head = ms(3, 4); prof->istft = ms(4, 5); prof->total = ms(0, 5);
-        prof->gemm_ms = 0; prof->gemm_flops = 0; prof->gemm_launches = (int) gemm_ev_flops_.size();
+        prof->gemm_ms = 0; prof->gemm_flops = 0; prof->gemm_bytes = gemm_bytes_; prof->gemm_launches = (int) gemm_ev_flops_.size();
         const bool log = std::getenv("MIO_TTS_B200_GEMM_LOG") != nullptr;
         for (size_t gi = 0; gi < gemm_ev_flops_.size(); ++gi) {
             auto & ef = gemm_ev_flops_[gi];

@@ -32,6 +32,7 @@ struct dbuf {
 struct stage_times {   // milliseconds of the last profiled run (CUDA events on the engine's stream)
     float prenet = 0, upsample_prior = 0, decoder = 0, post_head = 0, istft = 0, total = 0;
     double gemm_ms = 0, gemm_flops = 0; int gemm_launches = 0;
+    double gemm_bytes = 0;     // algorithmic DRAM bytes of those launches (A + W + out + residual)
     double attn_ms = 0; int attn_launches = 0;
 };
 
@@ -83,6 +84,7 @@ private:
     bool prof_gemm_ = false;
     stage_times * prof_ = nullptr;
     std::vector<std::pair<size_t, double>> gemm_ev_flops_;   // (event pair index, flops)
+    double gemm_bytes_ = 0;
     std::vector<size_t> attn_ev_;
     std::vector<std::array<int, 5>> gemm_ev_shape_;   // M, N, K, taps, epilogue
 

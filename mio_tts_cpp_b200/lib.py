@@ -27,7 +27,7 @@ class Profile(C.Structure):
     _fields_ = [("prenet_ms", C.c_float), ("upsample_prior_ms", C.c_float), ("decoder_ms", C.c_float),
                 ("post_head_ms", C.c_float), ("istft_ms", C.c_float), ("total_ms", C.c_float),
                 ("gemm_ms", C.c_double), ("gemm_flops", C.c_double), ("gemm_launches", C.c_int32),
-                ("attn_ms", C.c_double), ("attn_launches", C.c_int32)]
+                ("attn_ms", C.c_double), ("attn_launches", C.c_int32), ("gemm_bytes", C.c_double)]
 
 
 def lib_path():
