@@ -88,6 +88,8 @@ engine::engine(std::shared_ptr<model> m) : mdl(std::move(m)) {
     MIO_CUDA(cudaSetDevice(mdl->device));
     MIO_CUDA(cudaStreamCreateWithFlags(&st_, cudaStreamNonBlocking));
     for (auto & e : ev_) MIO_CUDA(cudaEventCreate(&e));
+    if (const char * e = std::getenv("MIO_TTS_B200_GRAPHS")) graphs_ok_ = !(e[0] == '0' && e[1] == '\0');
+    if (const char * e = std::getenv("MIO_TTS_B200_GRAPH_MAX_CODES")) graph_max_codes_ = (size_t) std::max(0, std::atoi(e));
 }
 
 engine::~engine() {
@@ -99,6 +101,7 @@ engine::~engine() {
     if (h_blob_) cudaFreeHost(h_blob_);
     if (rope_p_) cudaFree(rope_p_);
     if (rope_d_) cudaFree(rope_d_);
+    drop_graphs();
     for (auto & kv : istft_plans_) istft_plan_free(kv.second);
     for (auto & e : ev_) cudaEventDestroy(e);
     for (auto & e : gemm_ev_) cudaEventDestroy(e);
@@ -117,6 +120,7 @@ void engine::ensure(dbuf & b, size_t bytes) {
     b.cap = cap;
     tmaps_.clear();   // cached tensor maps may point at the freed buffer
     omaps_.clear();
+    drop_graphs();    // ... and so do the captured launch sequences
 }
 
 size_t engine::workspace_bytes() const {
@@ -134,6 +138,7 @@ void engine::ensure_rope(int prenet_pos, int decoder_pos) {
         const int cap = std::max(need, std::max(2048, have * 2));
         MIO_CUDA(cudaStreamSynchronize(st_));
         if (tab) { MIO_CUDA(cudaFree(tab)); tab = nullptr; }
+        drop_graphs();
         MIO_CUDA(cudaMalloc(&tab, (size_t) cap * (head_dim / 2) * sizeof(float2)));
         // theta_scale = powf(freq_base, -2/n_dims), computed on the host like ggml
         // (/root/reference/llama.cpp/ggml/src/ggml-cpu/ops.cpp:5616-5625, 5699-5716)
@@ -477,7 +482,76 @@ void engine::run_resblock(float *& x, float *& y, const seq_layout & L, const re
     gemm(act16_, rb.c2, L.rows, EPI_STORE32, x, c, 0, rb.c2.bias, x, c, nullptr, &L);
 }
 
+// Small batches are launch-bound (141 launches, ~9 us of host work each, against ~5 us of GPU work): the second time the
+// same batch shape (list of code counts + output format) comes by, its launch sequence is captured into a CUDA graph
+// and replayed from then on.  Kernel arguments depend only on the shape and on workspace addresses, so growing any
+// buffer drops the cached graphs; the per-batch tables reach the device through prepare()'s copy, outside the graph.
+void engine::drop_graphs() {
+    for (auto & kv : graphs_) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+    graphs_.clear();
+}
+
 void engine::run(bool with_istft, stage_times * prof, int stop_stage) {
+    size_t codes = 0;
+    for (int l : tok_.len) codes += (size_t) l;
+    if (!graphs_ok_ || !with_istft || prof != nullptr || stop_stage != 0 || codes > graph_max_codes_ || force_generic_attention) {
+        run_direct(with_istft, prof, stop_stage);
+        return;
+    }
+    MIO_CUDA(cudaSetDevice(mdl->device));
+    std::vector<int> key(tok_.len);
+    key.push_back(out_pcm16 ? 1 : 0);
+    gentry & g = graphs_[key];
+    g.last_use = ++graph_clock_;
+    if (g.exec != nullptr) {
+        MIO_CUDA(cudaGraphLaunch(g.exec, st_));
+        count_launch((int) g.kernels);
+        return;
+    }
+    if (g.seen++ == 0) {             // first sight: plain launches (this also sizes every buffer the shape needs)
+        if (graphs_.size() > 64) {   // forget the least recently used half
+            std::vector<std::pair<unsigned long long, std::vector<int>>> order;
+            for (auto & kv : graphs_) order.push_back({kv.second.last_use, kv.first});
+            std::sort(order.begin(), order.end());
+            for (size_t i = 0; i < order.size() / 2; ++i) {
+                auto it = graphs_.find(order[i].second);
+                if (it->second.exec) cudaGraphExecDestroy(it->second.exec);
+                graphs_.erase(it);
+            }
+        }
+        run_direct(with_istft, nullptr, 0);
+        return;
+    }
+    const unsigned long long n0 = g_launch_count.load();
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    bool ok = cudaStreamBeginCapture(st_, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+    if (ok) {
+        try {
+            run_direct(with_istft, nullptr, 0);
+        } catch (...) {
+            ok = false;
+        }
+        if (cudaStreamEndCapture(st_, &graph) != cudaSuccess || graph == nullptr) ok = false;
+    }
+    if (ok && cudaGraphInstantiate(&exec, graph, 0) != cudaSuccess) ok = false;
+    if (graph) cudaGraphDestroy(graph);
+    if (!ok) {                       // capture is not available here: stay on plain launches for good
+        cudaGetLastError();
+        if (exec) cudaGraphExecDestroy(exec);
+        graphs_ok_ = false;
+        drop_graphs();
+        g_launch_count.store(n0);
+        run_direct(with_istft, nullptr, 0);
+        return;
+    }
+    gentry & ge = graphs_[key];      // (run_direct cannot have dropped the map: every buffer already had its size)
+    ge.exec = exec;
+    ge.kernels = g_launch_count.load() - n0;
+    MIO_CUDA(cudaGraphLaunch(exec, st_));
+}
+
+void engine::run_direct(bool with_istft, stage_times * prof, int stop_stage) {
     const hparams & hp = mdl->hp;
     MIO_CUDA(cudaSetDevice(mdl->device));
     prof_ = prof;

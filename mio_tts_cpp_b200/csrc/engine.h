@@ -49,6 +49,7 @@ public:
                  size_t batch);
     // Device path over the prepared batch: decode -> spec (-> iSTFT -> peak normalise when with_istft).
     // stop_stage (debug): 1 prenet, 2 upsample, 3 prior, 4 decoder, 5 post -> stop there and expose that buffer
+    // (small repeated batch shapes are replayed from a captured CUDA graph: MIO_TTS_B200_GRAPHS=0 turns that off)
     void run(bool with_istft, stage_times * prof = nullptr, int stop_stage = 0);
     // dense fp32 copy of utterance 0 of the buffer exposed by a stopped run: [rows][cols]
     void fetch_debug(std::vector<float> & out, int & rows, int & cols);
@@ -113,6 +114,14 @@ private:
     std::map<std::pair<const void *, int>, CUtensorMap> tmaps_;
     std::map<std::array<uint64_t, 5>, CUtensorMap> omaps_;   // (ptr, rows, cols, ld, elem bytes) -> output map
     std::map<std::pair<int, int>, istft_plan> istft_plans_;
+
+    struct gentry { cudaGraphExec_t exec = nullptr; int seen = 0; unsigned long long kernels = 0, last_use = 0; };
+    std::map<std::vector<int>, gentry> graphs_;      // (code counts..., output format) -> captured launch sequence
+    bool graphs_ok_ = true;
+    size_t graph_max_codes_ = 4096;                  // larger batches are not launch-bound
+    unsigned long long graph_clock_ = 0;
+    void drop_graphs();
+    void run_direct(bool with_istft, stage_times * prof, int stop_stage);
 
     void ensure(dbuf & b, size_t bytes);
     void ensure_rope(int prenet_pos, int decoder_pos);

@@ -147,3 +147,29 @@ def test_micro_batcher_isolates_a_bad_request(tiny, emb):
             s.free()
     finally:
         tiny.enable_batching(0)
+
+
+def test_graph_replay_is_bit_exact(tiny, emb):
+    """Small repeated batch shapes are replayed from a captured CUDA graph (engine::run): the first call launches the
+    kernels one by one, the second captures them, later ones replay -- all must return the same samples, the launch
+    counter must keep counting the kernels inside the graph, and a different shape in between must not disturb it."""
+    c = _workload(1, 55, 40, 41)[0]
+    other = _workload(1, 56, 90, 91)[0]
+    outs, counts = [], []
+    for i in range(5):
+        n0 = tiny.launch_count()
+        outs.append(tiny.synthesize(c, emb)[0])
+        counts.append(tiny.launch_count() - n0)
+        if i == 2:
+            tiny.synthesize(other, emb)
+    for o in outs[1:]:
+        assert np.array_equal(o, outs[0])
+    assert len(set(counts)) == 1 and counts[0] > 20, counts
+    # the same utterance inside a batch (a different shape, plain launches) still matches
+    both, _ = tiny.synthesize_batch([other, c], [emb, emb])
+    assert np.array_equal(both[1], outs[0])
+    # WAV16 output is a different graph of the same shape
+    w1 = tiny.synthesize_wav16_batch([c], [emb])[0]
+    w2 = tiny.synthesize_wav16_batch([c], [emb])[0]
+    w3 = tiny.synthesize_wav16_batch([c], [emb])[0]
+    assert w1 == w2 == w3 == _wav16_rule(outs[0], tiny.sample_rate())
