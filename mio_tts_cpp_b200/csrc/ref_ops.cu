@@ -40,14 +40,13 @@ __device__ __forceinline__ float gelu_ggml(float x) {
 constexpr int C0_FRAMES = 128;   // conv0 output frames per block
 
 // ---- WavLM conv0 (1 -> C channels, kernel K <= 16, stride S, no bias; ggml_conv_1d rounds both operands to fp16,
-//      src/wavlm-extractor.cpp:664-667) evaluated on the fly; pass 1 accumulates per-channel (sum, sumsq) over time for
-//      the one-group-per-channel GroupNorm (:669-679), pass 2 recomputes, normalises, applies affine + GELU and writes
-//      fp16 rows.  Nothing fp32 of size [frames, C] ever touches HBM. ----
-template <bool APPLY>
+//      src/wavlm-extractor.cpp:664-667) evaluated on the fly from the waveform: the per-channel statistics of the
+//      one-group-per-channel GroupNorm over time (:669-679) come from wav_autocorr_kernel below, this kernel computes the
+//      convolution, normalises, applies affine + GELU and writes fp16 rows (generic K <= 16 / stride; the WavLM shape
+//      K = 10, S = 5 runs wav_conv0_apply_fast_kernel).  Nothing fp32 of size [frames, C] ever touches HBM. ----
 __global__ void __launch_bounds__(256) wav_conv0_kernel(const float * __restrict__ wav, const long long * __restrict__ wav_off,
                                                         const int * __restrict__ n_frames, const int * __restrict__ row0,
                                                         const float * __restrict__ w, int C, int K, int S,
-                                                        double * __restrict__ partial, int n_chunks,
                                                         const float2 * __restrict__ mean_rstd, const float * __restrict__ gw,
                                                         const float * __restrict__ gb, __half * __restrict__ out) {
     MIO_PDL_PROLOGUE();
@@ -67,53 +66,155 @@ __global__ void __launch_bounds__(256) wav_conv0_kernel(const float * __restrict
         float wk[16];
 #pragma unroll
         for (int j = 0; j < 16; ++j) wk[j] = j < K ? f16r(w[c * K + j]) : 0.0f;
-        if constexpr (!APPLY) {
-            double s = 0.0, q = 0.0;
-            for (int t = 0; t < nt; ++t) {
+        const float2 mr = mean_rstd[(size_t) clip * C + c];
+        const float a = gw[c] * mr.y, b = gb[c] - mr.x * mr.y * gw[c];
+        __half * o = out + ((size_t) row0[clip] + t0) * C + c;
+        for (int t = 0; t < C0_FRAMES; ++t) {
+            float v = 0.0f;
+            if (t < nt) {
                 float y = 0.0f;
 #pragma unroll
                 for (int j = 0; j < 16; ++j) if (j < K) y = fmaf(wk[j], xs[t * S + j], y);
-                s += (double) y;
-                q += (double) y * (double) y;
+                v = gelu_ggml(fmaf(y, a, b));
             }
-            double * p = partial + (((size_t) clip * n_chunks + chunk) * C + c) * 2;
-            p[0] = s; p[1] = q;
-        } else {
-            const float2 mr = mean_rstd[(size_t) clip * C + c];
-            const float a = gw[c] * mr.y, b = gb[c] - mr.x * mr.y * gw[c];
-            __half * o = out + ((size_t) row0[clip] + t0) * C + c;
-            for (int t = 0; t < C0_FRAMES; ++t) {
-                float v = 0.0f;
-                if (t < nt) {
-                    float y = 0.0f;
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) if (j < K) y = fmaf(wk[j], xs[t * S + j], y);
-                    v = gelu_ggml(fmaf(y, a, b));
-                }
-                o[(size_t) t * C] = __float2half_rn(v);   // padding rows of the clip are written as zeros
-            }
+            o[(size_t) t * C] = __float2half_rn(v);   // padding rows of the clip are written as zeros
         }
     }
 }
 
-// (sum, sumsq) partials -> (mean, rstd) per (clip, channel), summed in chunk order (deterministic);
-// ggml_group_norm: biased variance, eps inside the sqrt (ggml-cpu/ops.cpp:3955-4028)
-__global__ void wav_conv0_finalize_kernel(const double * __restrict__ partial, const int * __restrict__ n_frames, int C,
-                                          int n_chunks, float eps, float2 * __restrict__ mean_rstd, int n_clips) {
+// ---- conv0 statistics without evaluating the convolution: y_c[t] = sum_k w_c[k] x[S t + k], so over the frames of a clip
+//      sum_t y_c = w_c . s            with s[k]    = sum_t x[S t + k]
+//      sum_t y_c^2 = w_c^T R w_c      with R[k,k'] = sum_t x[S t + k] x[S t + k']
+//      -- K + K*K numbers per clip (fp16-rounded x like the convolution's operand, accumulated in double) instead of a
+//      pass of 2*K*C flops per frame.  partial[clip][chunk][a], a < K*K + K: a < K -> s[a], else R[(a-K)/K][(a-K)%K]. ----
+__global__ void __launch_bounds__(128) wav_autocorr_kernel(const float * __restrict__ wav, const long long * __restrict__ wav_off,
+                                                           const int * __restrict__ n_frames, int K, int S,
+                                                           double * __restrict__ partial, int n_chunks) {
     MIO_PDL_PROLOGUE();
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_clips * C) return;
-    const int clip = i / C, c = i - clip * C;
-    const int used = (n_frames[clip] + C0_FRAMES - 1) / C0_FRAMES;
-    double s = 0.0, q = 0.0;
-    for (int k = 0; k < used; ++k) {
-        const double * p = partial + (((size_t) clip * n_chunks + k) * C + c) * 2;
-        s += p[0]; q += p[1];
+    __shared__ float xs[C0_FRAMES * 8 + 32];
+    const int clip = blockIdx.y, chunk = blockIdx.x;
+    const int L = n_frames[clip];
+    const int t0 = chunk * C0_FRAMES;
+    if (t0 >= L) return;
+    const int nt = min(C0_FRAMES, L - t0);
+    const float * x = wav + wav_off[clip];
+    const int span = (nt - 1) * S + K;
+    for (int i = threadIdx.x; i < span; i += blockDim.x) xs[i] = f16r(x[(long long) t0 * S + i]);
+    __syncthreads();
+    const int NA = K * K + K;
+    double * p = partial + ((size_t) clip * n_chunks + chunk) * NA;
+    for (int a = threadIdx.x; a < NA; a += blockDim.x) {
+        double acc = 0.0;
+        if (a < K) {
+            for (int t = 0; t < nt; ++t) acc += (double) xs[t * S + a];
+        } else {
+            const int k = (a - K) / K, k2 = (a - K) - k * K;
+            for (int t = 0; t < nt; ++t) acc += (double) xs[t * S + k] * (double) xs[t * S + k2];
+        }
+        p[a] = acc;
     }
+}
+
+// (s, R) partials of a clip, summed in chunk order (deterministic) -> (mean, rstd) per channel;
+// ggml_group_norm: biased variance, eps inside the sqrt (ggml-cpu/ops.cpp:3955-4028)
+__global__ void __launch_bounds__(256) wav_conv0_moments_kernel(const double * __restrict__ partial, const int * __restrict__ n_frames,
+                                                                const float * __restrict__ w, int C, int K, int n_chunks, float eps,
+                                                                float2 * __restrict__ mean_rstd) {
+    MIO_PDL_PROLOGUE();
+    __shared__ double acc[16 * 16 + 16];
+    const int clip = blockIdx.x;
+    const int NA = K * K + K;
+    const int used = (n_frames[clip] + C0_FRAMES - 1) / C0_FRAMES;
+    for (int a = threadIdx.x; a < NA; a += blockDim.x) {
+        double v = 0.0;
+        for (int k = 0; k < used; ++k) v += partial[((size_t) clip * n_chunks + k) * NA + a];
+        acc[a] = v;
+    }
+    __syncthreads();
     const double n = (double) max(1, n_frames[clip]);
-    const double mean = s / n;
-    const double var = fmax(q / n - mean * mean, 0.0);
-    mean_rstd[i] = make_float2((float) mean, (float) (1.0 / sqrt(var + (double) eps)));
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        double wk[16];
+        for (int j = 0; j < K; ++j) wk[j] = (double) f16r(w[c * K + j]);
+        double s = 0.0, q = 0.0;
+        for (int j = 0; j < K; ++j) {
+            s += wk[j] * acc[j];
+            double row = 0.0;
+            for (int j2 = 0; j2 < K; ++j2) row += wk[j2] * acc[K + j * K + j2];
+            q += wk[j] * row;
+        }
+        const double mean = s / n;
+        const double var = fmax(q / n - mean * mean, 0.0);
+        mean_rstd[(size_t) clip * C + c] = make_float2((float) mean, (float) (1.0 / sqrt(var + (double) eps)));
+    }
+}
+
+// ---- conv0 + GroupNorm affine + GELU, register-tiled: a thread owns two adjacent channels (packed fp32x2 FMAs, one
+//      half2 store per frame) and walks the chunk four frames at a time (the 25 samples those frames touch come from
+//      shared memory as seven 16-byte loads).  K = 10, S = 5 (WavLM's first layer); other shapes use wav_conv0_kernel. ----
+typedef unsigned long long u64c;
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+    u64c d, ra, rb, rc;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(rc) : "f"(c.x), "f"(c.y));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(ra), "l"(rb), "l"(rc));
+    float2 r;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(d));
+    return r;
+}
+// the GEMM epilogue's GELU (act_apply, gemm_tcgen05.cu): ggml's fp16 table reproduced by two roundings, SFU tanh
+__device__ __forceinline__ float gelu_fast(float x) {
+    const float h = f16r(x);
+    const float u = 0.79788456080286535587989211986876f * h * (1.0f + 0.044715f * h * h);
+    const float t = 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * u));
+    const float y = f16r(0.5f * h * (1.0f + t));
+    return x <= -10.0f ? 0.0f : (x >= 10.0f ? x : y);
+}
+
+__global__ void __launch_bounds__(256) wav_conv0_apply_fast_kernel(const float * __restrict__ wav, const long long * __restrict__ wav_off,
+                                                                   const int * __restrict__ n_frames, const int * __restrict__ row0,
+                                                                   const float * __restrict__ w, int C,
+                                                                   const float2 * __restrict__ mean_rstd, const float * __restrict__ gw,
+                                                                   const float * __restrict__ gb, __half * __restrict__ out) {
+    MIO_PDL_PROLOGUE();
+    constexpr int K = 10, S = 5, TF = 4;
+    __shared__ __align__(16) float xs[C0_FRAMES * S + 32];
+    const int clip = blockIdx.y, chunk = blockIdx.x;
+    const int L = n_frames[clip];
+    const int t0 = chunk * C0_FRAMES;
+    if (t0 >= (L + C0_FRAMES - 1) / C0_FRAMES * C0_FRAMES) return;   // past this clip's (chunk-padded) extent
+    const int nt = max(0, min(C0_FRAMES, L - t0));                    // valid frames of this chunk
+    const float * x = wav + wav_off[clip];
+    const int span = nt > 0 ? (nt - 1) * S + K : 0;
+    for (int i = threadIdx.x; i < C0_FRAMES * S + 32; i += blockDim.x) xs[i] = i < span ? f16r(x[(long long) t0 * S + i]) : 0.0f;
+    __syncthreads();
+    for (int cp = threadIdx.x; cp < (C >> 1); cp += blockDim.x) {
+        const int c = cp * 2;
+        float2 wk[K];
+#pragma unroll
+        for (int j = 0; j < K; ++j) wk[j] = make_float2(f16r(w[c * K + j]), f16r(w[(c + 1) * K + j]));
+        const float2 m0 = mean_rstd[(size_t) clip * C + c], m1 = mean_rstd[(size_t) clip * C + c + 1];
+        const float2 sc = make_float2(gw[c] * m0.y, gw[c + 1] * m1.y);
+        const float2 sh = make_float2(gb[c] - m0.x * m0.y * gw[c], gb[c + 1] - m1.x * m1.y * gw[c + 1]);
+        __half2 * o = reinterpret_cast<__half2 *>(out + ((size_t) row0[clip] + t0) * C + c);
+        for (int t = 0; t < C0_FRAMES; t += TF) {
+            float xv[28];
+#pragma unroll
+            for (int i = 0; i < 7; ++i) {
+                const float4 v = *reinterpret_cast<const float4 *>(xs + t * S + 4 * i);
+                xv[4 * i] = v.x; xv[4 * i + 1] = v.y; xv[4 * i + 2] = v.z; xv[4 * i + 3] = v.w;
+            }
+#pragma unroll
+            for (int f = 0; f < TF; ++f) {
+                float2 y = make_float2(0.0f, 0.0f);
+#pragma unroll
+                for (int j = 0; j < K; ++j) y = ffma2(wk[j], make_float2(xv[f * S + j], xv[f * S + j]), y);
+                y = ffma2(y, sc, sh);
+                const bool live = t + f < nt;                  // padding rows of the clip are written as zeros
+                o[(size_t) (t + f) * (C >> 1)] = __floats2half2_rn(live ? gelu_fast(y.x) : 0.0f, live ? gelu_fast(y.y) : 0.0f);
+            }
+        }
+    }
 }
 
 // ---- row relayout + cast: dst row r takes src row map[r] (or zeros when map[r] < 0), scaled, as fp32 and/or 16-bit ----
@@ -341,27 +442,24 @@ void launch_wav_prepare(const float * src, const long long * src_off, const int 
 
 int wav_conv0_chunk_frames() { return C0_FRAMES; }
 
-void launch_wav_conv0_stats(const float * wav, const long long * wav_off, const int * n_frames, const float * w, int C, int K,
-                            int S, double * partial, int n_chunks, int n_clips, cudaStream_t st) {
+void launch_wav_conv0_moments(const float * wav, const long long * wav_off, const int * n_frames, const float * w, int C, int K,
+                              int S, double * partial, int n_chunks, float eps, float2 * mean_rstd, int n_clips, cudaStream_t st) {
     if (K > 16 || (C0_FRAMES - 1) * S + K > C0_FRAMES * 8 + 32) throw cuda_error("wavlm conv0: unsupported kernel/stride");
-    launch_pdl(wav_conv0_kernel<false>, dim3(n_chunks, n_clips), dim3(256), 0, st, wav, wav_off, n_frames, (const int *) nullptr,
-               w, C, K, S, partial, n_chunks, (const float2 *) nullptr, (const float *) nullptr, (const float *) nullptr,
-               (__half *) nullptr);
-    count_launch();
-}
-
-void launch_wav_conv0_finalize(const double * partial, const int * n_frames, int C, int n_chunks, float eps,
-                               float2 * mean_rstd, int n_clips, cudaStream_t st) {
-    launch_pdl(wav_conv0_finalize_kernel, dim3(blocks_for((size_t) n_clips * C, 128)), dim3(128), 0, st, partial, n_frames, C,
-               n_chunks, eps, mean_rstd, n_clips);
-    count_launch();
+    launch_pdl(wav_autocorr_kernel, dim3(n_chunks, n_clips), dim3(128), 0, st, wav, wav_off, n_frames, K, S, partial, n_chunks);
+    launch_pdl(wav_conv0_moments_kernel, dim3(n_clips), dim3(256), 0, st, (const double *) partial, n_frames, w, C, K, n_chunks, eps,
+               mean_rstd);
+    count_launch(2);
 }
 
 void launch_wav_conv0_apply(const float * wav, const long long * wav_off, const int * n_frames, const int * row0,
                             const float * w, int C, int K, int S, int n_chunks, const float2 * mean_rstd, const float * gw,
                             const float * gb, void * out16, int n_clips, cudaStream_t st) {
-    launch_pdl(wav_conv0_kernel<true>, dim3(n_chunks, n_clips), dim3(256), 0, st, wav, wav_off, n_frames, row0, w, C, K, S,
-               (double *) nullptr, n_chunks, mean_rstd, gw, gb, (__half *) out16);
+    if (K == 10 && S == 5 && (C & 1) == 0)
+        launch_pdl(wav_conv0_apply_fast_kernel, dim3(n_chunks, n_clips), dim3(256), 0, st, wav, wav_off, n_frames, row0, w, C,
+                   mean_rstd, gw, gb, (__half *) out16);
+    else
+        launch_pdl(wav_conv0_kernel, dim3(n_chunks, n_clips), dim3(256), 0, st, wav, wav_off, n_frames, row0, w, C, K, S,
+                   mean_rstd, gw, gb, (__half *) out16);
     count_launch();
 }
 

@@ -529,7 +529,7 @@ void refenc::prepare(const float * const * pcm, const size_t * n, int sample_rat
     ensure(src_, (size_t) so * 4);
     ensure(wav_, (size_t) wo * 4 + 256);
     ensure(peak_, batch * 4);
-    ensure(part_, batch * (size_t) n_chunks_ * C * 2 * sizeof(double));
+    ensure(part_, batch * (size_t) n_chunks_ * (16 * 16 + 16) * sizeof(double));   // (s, R) partials of the conv0 statistics
     ensure(mr_, batch * (size_t) C * sizeof(float2));
     for (int i = 0; i < 6; ++i) ensure(lvl_[i], ((size_t) (rows0_ >> i) + 256) * C * 2);
     ensure(c6_, ((size_t) (rows0_ >> 6) + 256) * C * 4);
@@ -584,9 +584,8 @@ void refenc::run_wavlm() {
     // front end + conv0 + GroupNorm over time + GELU -> level 0 (fp16)
     launch_wav_prepare((const float *) src_.p, d_src_off_, d_n_src_, (float *) wav_.p, d_wav_off_, d_n_wav_, (unsigned int *) peak_.p,
                        src_rate_, hp.sample_rate, n, max_nsrc, max_nwav, st_);
-    launch_wav_conv0_stats((const float *) wav_.p, d_wav_off_, d_len0_, M.conv0_w, C, hp.conv_kernel[0], hp.conv_stride[0],
-                           (double *) part_.p, n_chunks_, n, st_);
-    launch_wav_conv0_finalize((const double *) part_.p, d_len0_, C, n_chunks_, hp.norm_eps, (float2 *) mr_.p, n, st_);
+    launch_wav_conv0_moments((const float *) wav_.p, d_wav_off_, d_len0_, M.conv0_w, C, hp.conv_kernel[0], hp.conv_stride[0],
+                             (double *) part_.p, n_chunks_, hp.norm_eps, (float2 *) mr_.p, n, st_);
     launch_wav_conv0_apply((const float *) wav_.p, d_wav_off_, d_len0_, d_row0_l0_, M.conv0_w, C, hp.conv_kernel[0], hp.conv_stride[0],
                            n_chunks_, (const float2 *) mr_.p, M.conv0_norm.w, M.conv0_norm.b, lvl_[0].p, n, st_);
     // conv1..6: stride-2 convolutions as implicit GEMMs over the pair view of the previous level, GELU in the epilogue

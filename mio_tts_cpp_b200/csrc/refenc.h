@@ -156,10 +156,9 @@ int wav_conv0_chunk_frames();
 void launch_wav_prepare(const float * src, const long long * src_off, const int * n_src, float * wav, const long long * wav_off,
                         const int * n_wav, unsigned int * peak_bits, int rate_in, int rate_out, int n_clips, int max_n_src,
                         int max_n_wav, cudaStream_t st);
-void launch_wav_conv0_stats(const float * wav, const long long * wav_off, const int * n_frames, const float * w, int C, int K,
-                            int S, double * partial, int n_chunks, int n_clips, cudaStream_t st);
-void launch_wav_conv0_finalize(const double * partial, const int * n_frames, int C, int n_chunks, float eps,
-                               float2 * mean_rstd, int n_clips, cudaStream_t st);
+// statistics through the clip's autocorrelation (K + K*K sums per clip) instead of a convolution pass
+void launch_wav_conv0_moments(const float * wav, const long long * wav_off, const int * n_frames, const float * w, int C, int K,
+                              int S, double * partial, int n_chunks, float eps, float2 * mean_rstd, int n_clips, cudaStream_t st);
 void launch_wav_conv0_apply(const float * wav, const long long * wav_off, const int * n_frames, const int * row0,
                             const float * w, int C, int K, int S, int n_chunks, const float2 * mean_rstd, const float * gw,
                             const float * gb, void * out16, int n_clips, cudaStream_t st);
