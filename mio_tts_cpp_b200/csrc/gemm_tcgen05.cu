@@ -131,6 +131,12 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap * map, uint32_t s
                  ::"l"((uint64_t) map), "r"(src), "r"(c0), "r"(c1)
                  : "memory");
 }
+// out[box] += smem[box], the addition performed by the L2 (one rounding per element, like a read-add-write in the SM)
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap * map, uint32_t src, int c0, int c1) {
+    asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"((uint64_t) map), "r"(src), "r"(c0), "r"(c1)
+                 : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N> __device__ __forceinline__ void bulk_wait_read() {   // smem of all but the N newest stores is reusable
     asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
@@ -268,24 +274,29 @@ __device__ __forceinline__ void chunk_store32(const gemm_args & a, const uint32_
     }
 }
 
+template <bool GUARD>
+__device__ __forceinline__ void chunk_store32_pick(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, int lane, int n,
+                                                   const float * gate_row, bool has_res) {
+    if (a.gate) {
+        if (has_res) { if (a.bias) chunk_store32<true, true, true, GUARD>(a, raw, buf, lane, n, gate_row);
+                       else chunk_store32<false, true, true, GUARD>(a, raw, buf, lane, n, gate_row); }
+        else { if (a.bias) chunk_store32<true, true, false, GUARD>(a, raw, buf, lane, n, gate_row);
+               else chunk_store32<false, true, false, GUARD>(a, raw, buf, lane, n, gate_row); }
+    } else if (has_res) {
+        if (a.bias) chunk_store32<true, false, true, GUARD>(a, raw, buf, lane, n, gate_row);
+        else chunk_store32<false, false, true, GUARD>(a, raw, buf, lane, n, gate_row);
+    } else {
+        if (a.bias) chunk_store32<true, false, false, GUARD>(a, raw, buf, lane, n, gate_row);
+        else chunk_store32<false, false, false, GUARD>(a, raw, buf, lane, n, gate_row);
+    }
+}
+
+// warp-uniform dispatch to the term combinations in use; has_res: the residual sits in the box and is added here
+// (false in reduce-add mode, where the box carries the new term alone)
 __device__ __forceinline__ void chunk_store32_any(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, int lane, int n,
                                                   const float * gate_row, bool has_res) {
-    // warp-uniform dispatch to the term combinations the decoder uses
-    if (n + 32 <= a.N) {
-        if (a.gate) { if (a.bias) chunk_store32<true, true, true, false>(a, raw, buf, lane, n, gate_row);
-                      else chunk_store32<false, true, true, false>(a, raw, buf, lane, n, gate_row); }
-        else if (has_res) { if (a.bias) chunk_store32<true, false, true, false>(a, raw, buf, lane, n, gate_row);
-                            else chunk_store32<false, false, true, false>(a, raw, buf, lane, n, gate_row); }
-        else { if (a.bias) chunk_store32<true, false, false, false>(a, raw, buf, lane, n, gate_row);
-               else chunk_store32<false, false, false, false>(a, raw, buf, lane, n, gate_row); }
-    } else {
-        if (a.gate) { if (a.bias) chunk_store32<true, true, true, true>(a, raw, buf, lane, n, gate_row);
-                      else chunk_store32<false, true, true, true>(a, raw, buf, lane, n, gate_row); }
-        else if (has_res) { if (a.bias) chunk_store32<true, false, true, true>(a, raw, buf, lane, n, gate_row);
-                            else chunk_store32<false, false, true, true>(a, raw, buf, lane, n, gate_row); }
-        else { if (a.bias) chunk_store32<true, false, false, true>(a, raw, buf, lane, n, gate_row);
-               else chunk_store32<false, false, false, true>(a, raw, buf, lane, n, gate_row); }
-    }
+    if (n + 32 <= a.N) chunk_store32_pick<false>(a, raw, buf, lane, n, gate_row, has_res);
+    else chunk_store32_pick<true>(a, raw, buf, lane, n, gate_row, has_res);
 }
 
 template <bool BF16> __device__ __forceinline__ uint32_t pack16t(float a, float b) {
@@ -494,7 +505,10 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
         const uint32_t ebuf = smem_base + C::STAGES * C::STAGE_BYTES + ew * E::WARP_BYTES;
         const uint32_t rope_st = ebuf + EPI_NBUF * E::BUF_BYTES;
         auto rbar = [&](int b) { return bar_base + 256u + 8u * (ew * EPI_NBUF + b); };
-        const bool has_res = EPI == EPI_STORE32 && a.res != nullptr;
+        // in-place fp32 residual: either read back through TMA, added in registers and stored (has_res), or -- red_add --
+        // left where it is and updated by a TMA reduce-add of the new term alone (no residual bytes cross L2 -> SM)
+        const bool red_add = EPI == EPI_STORE32 && a.res != nullptr && a.red_add != 0;
+        const bool has_res = EPI == EPI_STORE32 && a.res != nullptr && !red_add;
 
         auto tile_row0 = [&](int t) { return (t / num_n_tiles) * TILE_M + cta_rank * BLOCK_M + quad * 32; };
         auto chunk_ok = [&](int t, int c) {
@@ -605,7 +619,8 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
                 fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) {
-                    tma_store_2d(&a.map_out, buf, EPI == EPI_SWIGLU16 ? (n >> 1) : n, row0);
+                    if (red_add) tma_reduce_add_2d(&a.map_out, buf, n, row0);
+                    else tma_store_2d(&a.map_out, buf, EPI == EPI_SWIGLU16 ? (n >> 1) : n, row0);
                     bulk_commit();
                     if (has_res) {
                         // the box of chunk nch-1 is the next prefetch target: its store must have read smem
@@ -745,6 +760,7 @@ void gemm_launch(const gemm_args & a, int num_sms, cudaStream_t st) {
     if (a.M <= 0 || a.N <= 0 || a.K <= 0) return;
     if (a.epilogue == EPI_ROPE16 && (a.head_dim % 32) != 0) throw cuda_error("gemm: rope epilogue needs head_dim % 32 == 0");
     if (a.res != nullptr && a.res != a.out) throw cuda_error("gemm: the residual must be the (in-place) output");
+    static const bool use_red = [] { const char * e = std::getenv("MIO_TTS_B200_GEMM_RED"); return !(e && e[0] == '0'); }();
     static int ew = -1, ncta = -1;
     if (ew < 0) {   // epilogue warps per TMEM lane quadrant
         const char * e = std::getenv("MIO_TTS_B200_GEMM_EW");
@@ -753,11 +769,13 @@ void gemm_launch(const gemm_args & a, int num_sms, cudaStream_t st) {
         const char * c = std::getenv("MIO_TTS_B200_GEMM_CTA");   // 1 = single-CTA tiles everywhere (A/B testing)
         ncta = (c && std::atoi(c) == 1) ? 1 : 2;
     }
+    gemm_args g = a;
+    g.red_add = (use_red && a.res != nullptr && a.epilogue == EPI_STORE32) ? 1 : 0;
     if (gemm_block_n(a.N) == 256) {
-        if (ncta == 2) { if (ew == 1) launch_bn<256, 1, 2>(a, num_sms, st); else launch_bn<256, 2, 2>(a, num_sms, st); }
-        else { if (ew == 1) launch_bn<256, 1, 1>(a, num_sms, st); else launch_bn<256, 2, 1>(a, num_sms, st); }
+        if (ncta == 2) { if (ew == 1) launch_bn<256, 1, 2>(g, num_sms, st); else launch_bn<256, 2, 2>(g, num_sms, st); }
+        else { if (ew == 1) launch_bn<256, 1, 1>(g, num_sms, st); else launch_bn<256, 2, 1>(g, num_sms, st); }
     } else {
-        if (ew == 1) launch_bn<128, 1, 1>(a, num_sms, st); else launch_bn<128, 2, 1>(a, num_sms, st);
+        if (ew == 1) launch_bn<128, 1, 1>(g, num_sms, st); else launch_bn<128, 2, 1>(g, num_sms, st);
     }
 }
 
