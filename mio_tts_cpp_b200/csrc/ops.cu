@@ -48,44 +48,79 @@ __global__ void gather_kernel(const float * __restrict__ table, const int * __re
 
 // ---- AdaLN conditioning: p = W * silu(emb) + b for every conditioned norm at once
 //      (src/miocodec-decoder.cpp:1164-1181 cond = silu(embedding); :1204-1210, :1271-1277, :1390-1400) ----
-// Block = 64 utterances x 16 output rows: silu(emb) of the 64 utterances and the 16 weight rows are staged in shared
-// memory once, each thread owns one utterance and 4 consecutive rows (weight reads are warp broadcasts, embedding
-// reads are conflict-free through the +1 row padding).
-constexpr int COND_UTT = 64, COND_ROWS = 16;
+// Block = 64 utterances x 64 output rows staged in shared memory (silu(emb) once per block); a thread owns a 4 x 4
+// (utterance, row) tile and walks k four at a time with 16-byte loads: 8 loads per 64 FMAs instead of 5 per 4.  Every
+// accumulator still sums k = 0 .. adim-1 in order, like the reference's dot product.
+constexpr int COND_UTT = 64, COND_ROWS = 64;
 __global__ void __launch_bounds__(256) cond_kernel(const float * __restrict__ w, const float * __restrict__ b,
                                                    const float * __restrict__ emb, float * __restrict__ out, int n_out,
                                                    int adim, int n_utt) {
     MIO_PDL_PROLOGUE();
-    extern __shared__ float cond_smem[];
-    float * es = cond_smem;                                  // [COND_UTT][adim + 1]
-    float * ws = cond_smem + COND_UTT * (adim + 1);          // [COND_ROWS][adim]
+    extern __shared__ __align__(16) float cond_smem[];
+    const int ld = adim + 4;                                 // +4 floats: 16-byte rows that do not all start in bank 0
+    float * es = cond_smem;                                  // [COND_UTT][ld]
+    float * ws = cond_smem + COND_UTT * ld;                  // [COND_ROWS][ld]
     const int utt0 = blockIdx.y * COND_UTT, j0 = blockIdx.x * COND_ROWS;
-    for (int i = threadIdx.x; i < COND_UTT * adim; i += blockDim.x) {
-        const int u = i / adim, k = i - u * adim;
-        es[u * (adim + 1) + k] = utt0 + u < n_utt ? silu_exact(emb[(size_t) (utt0 + u) * adim + k]) : 0.0f;
+    // staging: 16-byte loads, several in flight per thread (one scalar load per iteration left the block latency-bound)
+    const int a4 = adim >> 2;
+    const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll 4
+    for (int i = threadIdx.x; i < COND_UTT * a4; i += blockDim.x) {
+        const int u = i / a4, k4 = i - u * a4;
+        float4 v = utt0 + u < n_utt ? __ldg(reinterpret_cast<const float4 *>(emb + (size_t) (utt0 + u) * adim) + k4) : zero4;
+        if (utt0 + u < n_utt) { v.x = silu_exact(v.x); v.y = silu_exact(v.y); v.z = silu_exact(v.z); v.w = silu_exact(v.w); }
+        *reinterpret_cast<float4 *>(es + u * ld + 4 * k4) = v;
     }
-    for (int i = threadIdx.x; i < COND_ROWS * adim; i += blockDim.x) {
-        const int r = i / adim;
-        ws[i] = j0 + r < n_out ? __ldg(w + (size_t) j0 * adim + i) : 0.0f;
+#pragma unroll 4
+    for (int i = threadIdx.x; i < COND_ROWS * a4; i += blockDim.x) {
+        const int r = i / a4, k4 = i - r * a4;
+        *reinterpret_cast<float4 *>(ws + r * ld + 4 * k4) =
+            j0 + r < n_out ? __ldg(reinterpret_cast<const float4 *>(w + (size_t) (j0 + r) * adim) + k4) : zero4;
     }
     __syncthreads();
-    const int u = threadIdx.x & (COND_UTT - 1), jg = threadIdx.x / COND_UTT;
-    const float * e = es + u * (adim + 1);
-    const float * wr = ws + jg * 4 * adim;
-    float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-    for (int k = 0; k < adim; ++k) {
-        const float ev = e[k];
+    const int ug = threadIdx.x & 15, rg = threadIdx.x >> 4;  // utterances ug + 16*u (conflict-free 16-byte reads: ld/4 is odd), rows 4*rg .. +3
+    float acc[4][4];
 #pragma unroll
-        for (int r = 0; r < 4; ++r) acc[r] = fmaf(wr[r * adim + k], ev, acc[r]);
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int r = 0; r < 4; ++r) acc[u][r] = 0.0f;
+    for (int k = 0; k < adim; k += 4) {
+        float4 e4[4], w4[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) e4[u] = *reinterpret_cast<const float4 *>(es + (ug + 16 * u) * ld + k);
+#pragma unroll
+        for (int r = 0; r < 4; ++r) w4[r] = *reinterpret_cast<const float4 *>(ws + (4 * rg + r) * ld + k);
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                acc[u][r] = fmaf(w4[r].x, e4[u].x, acc[u][r]);
+                acc[u][r] = fmaf(w4[r].y, e4[u].y, acc[u][r]);
+                acc[u][r] = fmaf(w4[r].z, e4[u].z, acc[u][r]);
+                acc[u][r] = fmaf(w4[r].w, e4[u].w, acc[u][r]);
+            }
     }
-    if (utt0 + u >= n_utt) return;
-    const int j = j0 + jg * 4;
-    float * o = out + (size_t) (utt0 + u) * n_out + j;
-    if (j + 4 <= n_out && (n_out & 3) == 0) {
-        *reinterpret_cast<float4 *>(o) = make_float4(acc[0] + b[j], acc[1] + b[j + 1], acc[2] + b[j + 2], acc[3] + b[j + 3]);
-    } else {
+    // stage the 64 x 64 result tile (over the embeddings, which are dead now) and write 256-byte row segments: the
+    // per-thread float4s would land 100 KB apart
+    __syncthreads();
+    float * os = cond_smem;                                  // [COND_UTT][COND_ROWS + 4]
+    constexpr int OLD = COND_ROWS + 4;
 #pragma unroll
-        for (int r = 0; r < 4; ++r) if (j + r < n_out) o[r] = acc[r] + b[j + r];
+    for (int u = 0; u < 4; ++u)
+        *reinterpret_cast<float4 *>(os + (ug + 16 * u) * OLD + 4 * rg) = make_float4(acc[u][0], acc[u][1], acc[u][2], acc[u][3]);
+    __syncthreads();
+    for (int i = threadIdx.x; i < COND_UTT * (COND_ROWS / 4); i += blockDim.x) {
+        const int u = i / (COND_ROWS / 4), c4 = i - u * (COND_ROWS / 4);
+        const int utt = utt0 + u, j = j0 + 4 * c4;
+        if (utt >= n_utt || j >= n_out) continue;
+        const float4 v = *reinterpret_cast<const float4 *>(os + u * OLD + 4 * c4);
+        float * o = out + (size_t) utt * n_out + j;
+        if (j + 4 <= n_out && (n_out & 3) == 0) {
+            *reinterpret_cast<float4 *>(o) = make_float4(v.x + b[j], v.y + b[j + 1], v.z + b[j + 2], v.w + b[j + 3]);
+        } else {
+            const float vv[4] = {v.x, v.y, v.z, v.w};
+            for (int r = 0; r < 4; ++r) if (j + r < n_out) o[r] = vv[r] + b[j + r];
+        }
     }
 }
 
@@ -114,17 +149,23 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float * __restrict
 #pragma unroll
         for (int i = 0; i < NV; ++i) v[r][i] = xr[lane + 32 * i];
     }
-    float4 pa[NV], pb[NV];      // (scale, shift) or (weight, bias)
+    // hoisting costs 8*NV registers: wider rows fetch each parameter where it is used instead (occupancy matters more there)
+    constexpr bool HOIST = NV <= 4;
+    float4 pa[HOIST ? NV : 1], pb[HOIST ? NV : 1];      // (scale, shift) or (weight, bias)
+    auto param_ptrs = [&](int u, const float4 *& a4, const float4 *& b4) {
+        a4 = cond ? reinterpret_cast<const float4 *>(cond + (size_t) max(u, 0) * cond_ld + scale_off) : reinterpret_cast<const float4 *>(w);
+        b4 = cond ? reinterpret_cast<const float4 *>(cond + (size_t) max(u, 0) * cond_ld + shift_off) : reinterpret_cast<const float4 *>(b);
+    };
     auto load_params = [&](int u) {
-        const float4 * a4 = cond ? reinterpret_cast<const float4 *>(cond + (size_t) max(u, 0) * cond_ld + scale_off)
-                                 : reinterpret_cast<const float4 *>(w);
-        const float4 * b4 = cond ? reinterpret_cast<const float4 *>(cond + (size_t) max(u, 0) * cond_ld + shift_off)
-                                 : reinterpret_cast<const float4 *>(b);
+        if constexpr (HOIST) {
+            const float4 * a4, * b4;
+            param_ptrs(u, a4, b4);
 #pragma unroll
-        for (int i = 0; i < NV; ++i) { pa[i] = __ldg(a4 + lane + 32 * i); pb[i] = __ldg(b4 + lane + 32 * i); }
+            for (int i = 0; i < NV; ++i) { pa[i] = __ldg(a4 + lane + 32 * i); pb[i] = __ldg(b4 + lane + 32 * i); }
+        }
     };
     const bool affine = cond != nullptr || w != nullptr;
-    if (affine) load_params(utt[0]);
+    if (HOIST && affine) load_params(utt[0]);
     float rstd[RW];
 #pragma unroll
     for (int r = 0; r < RW; ++r) {
@@ -145,17 +186,24 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float * __restrict
     for (int r = 0; r < RW; ++r) {
         const int row = row0 + r;
         if (row >= rows) break;
-        if (r > 0 && cond && utt[r] != utt[r - 1]) load_params(utt[r]);
+        if (HOIST && r > 0 && cond && utt[r] != utt[r - 1]) load_params(utt[r]);
+        const float4 * a4 = nullptr, * b4 = nullptr;
+        if (!HOIST && affine) param_ptrs(utt[r], a4, b4);
 #pragma unroll
         for (int i = 0; i < NV; ++i) {
             const int c4 = lane + 32 * i;
             float4 y = make_float4(v[r][i].x * rstd[r], v[r][i].y * rstd[r], v[r][i].z * rstd[r], v[r][i].w * rstd[r]);
+            float4 A = make_float4(0.f, 0.f, 0.f, 0.f), B = A;
+            if (affine) {
+                if constexpr (HOIST) { A = pa[i]; B = pb[i]; }
+                else { A = __ldg(a4 + c4); B = __ldg(b4 + c4); }
+            }
             if (cond) {
-                y.x = y.x * (pa[i].x + 1.0f) + pb[i].x; y.y = y.y * (pa[i].y + 1.0f) + pb[i].y;
-                y.z = y.z * (pa[i].z + 1.0f) + pb[i].z; y.w = y.w * (pa[i].w + 1.0f) + pb[i].w;
+                y.x = y.x * (A.x + 1.0f) + B.x; y.y = y.y * (A.y + 1.0f) + B.y;
+                y.z = y.z * (A.z + 1.0f) + B.z; y.w = y.w * (A.w + 1.0f) + B.w;
             } else if (w) {
-                y.x = y.x * pa[i].x + pb[i].x; y.y = y.y * pa[i].y + pb[i].y;
-                y.z = y.z * pa[i].z + pb[i].z; y.w = y.w * pa[i].w + pb[i].w;
+                y.x = y.x * A.x + B.x; y.y = y.y * A.y + B.y;
+                y.z = y.z * A.z + B.z; y.w = y.w * A.w + B.w;
             }
             if (utt[r] < 0) y = make_float4(0.f, 0.f, 0.f, 0.f);   // gap row of the layout
             if (out32) reinterpret_cast<float4 *>(out32 + (size_t) row * DIM)[c4] = y;
@@ -446,7 +494,8 @@ void launch_cond(const float * w, const float * b, const float * emb, float * ou
                  cudaStream_t st) {
     if (n_out <= 0 || n_utt <= 0) return;
     dim3 grid(blocks_for((size_t) n_out, COND_ROWS), (unsigned) ((n_utt + COND_UTT - 1) / COND_UTT));
-    const size_t smem = ((size_t) COND_UTT * (adim + 1) + (size_t) COND_ROWS * adim) * sizeof(float);
+    if (adim & 3) throw cuda_error("cond: adanorm dimension must be a multiple of 4");
+    const size_t smem = (size_t) (COND_UTT + COND_ROWS) * (adim + 4) * sizeof(float);
     if (smem > 200 * 1024) throw cuda_error("cond: adanorm dimension too large");
     static bool configured[64] = {false};
     int dev = 0;
