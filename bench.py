@@ -144,6 +144,9 @@ def run_b200(args, rank, world, local_rank):
     total_audio = sum_over_ranks(audio_s_per_step)
     value = total_audio / (ms * 1e-3)
 
+    # per-launch GEMM timings for the roofline, taken right after the timed region (same clocks and power state)
+    profs = [m.profile_resident() for _ in range(3)] if rank == 0 else []
+
     # ---- end to end through the public batch call: host codes in, host (pinned) waveforms out, every step.
     # Like the reference server's slots (tts-mio-server.cpp:2659-2670, one context clone per slot), `--e2e-slots`
     # host threads each own a clone of the context (shared weights, own stream + workspace) and each call
@@ -211,7 +214,6 @@ def run_b200(args, rank, world, local_rank):
     if rank == 0:
         # ---- roofline of the dominant kernel (the tcgen05 GEMM family), timed live with CUDA events per launch ----
         peaks = U.measured_peaks()
-        profs = [m.profile_resident() for _ in range(3)]
         p = profs[-1]
         g_ms = float(np.median([q["gemm_ms"] for q in profs]))
         achieved = p["gemm_flops"] / (g_ms * 1e-3) / 1e12
