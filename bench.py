@@ -93,7 +93,13 @@ def run_b200(args, rank, world, local_rank):
     from mio_tts_cpp_b200 import MioTTS
 
     dist = None
+    json_fd = None
     if world > 1:
+        # stdout carries exactly one JSON line, but NCCL writes its banner ("NCCL version ...") to fd 1 from C: keep a
+        # private duplicate of the real stdout for the JSON line and point fd 1 at stderr for everything else
+        sys.stdout.flush()
+        json_fd = os.dup(1)
+        os.dup2(2, 1)
         import torch.distributed as dist_mod
 
         torch.cuda.set_device(local_rank)
@@ -242,7 +248,10 @@ def run_b200(args, rank, world, local_rank):
             line["cpu_baseline"] = {"value": v, "unit": "audio-seconds/s", "cores": cores, "kind": kind,
                                     "sample": f"{n_cpu} of the 64 utterances x {N_CODES} codes, sequential "
                                               f"mio_tts_synthesize calls, {cores} threads, {dt:.1f} s"}
-        print(json.dumps(line), flush=True)
+        if json_fd is None:
+            print(json.dumps(line), flush=True)
+        else:
+            os.write(json_fd, (json.dumps(line) + "\n").encode())
     barrier()
     m.free()
     if dist is not None:
