@@ -169,7 +169,7 @@ MIO_B200_API void mio_tts_b200_wav_free(uint8_t * wav);
  * released by the previous batch to come back; `workers` engines (default 4) overlap one batch's device -> host copy with
  * the next batch's kernels.  Results are bit-identical to un-batched calls; a request that fails (e.g. an out-of-range
  * code) fails alone with its usual message.  max_batch <= 0 turns batching off for this context.
- * mio_tts_reserve_workspace(ctx, n_codes) then also sizes every worker for max_batch utterances of n_codes.
+ * mio_tts_reserve_workspace(ctx, n_codes) then also sizes every worker for max_batch utterances of n_codes (at most 32 k codes each).
  * MIO_TTS_B200_BATCHING="max_batch[,max_wait_us[,workers]]" enables it at mio_tts_init_from_file without code changes. */
 MIO_B200_API bool mio_tts_b200_context_enable_batching(struct mio_tts_context * ctx, int32_t max_batch, int32_t max_wait_us,
                                                        int32_t workers, char * err, size_t err_size);

@@ -73,9 +73,12 @@ batcher::~batcher() {
 }
 
 void batcher::reserve(int n_codes) {
+    // at most 32 k codes per worker up front (~3 GB each): longer batches still grow the workspace on demand
+    const int n = std::max(1, n_codes);
+    const int batch = std::max(1, std::min(max_batch, 32768 / n));
     for (auto & e : eng_) {
         std::lock_guard<std::mutex> lk(e->mtx);
-        e->reserve(n_codes, max_batch);
+        e->reserve(n, batch);
     }
 }
 

@@ -59,7 +59,7 @@ private:
     size_t expect_ = 1;          // callers released by the batch that finished last: a gathering worker waits (bounded) for them
     size_t busy_codes_ = 0;      // codes of the batches whose kernels are running
     size_t sat_codes_ = 4096;    // admission threshold: ~10 utterances of 400 codes keep the GPU busy
-    size_t max_codes_ = 1 << 17; // bound on the codes of one batch (workspace ~ 100 KB per code)
+    size_t max_codes_ = 1 << 16; // bound on the codes of one batch (workspace ~ 100 KB per code: 6.5 GB per worker at most)
     bool stop_ = false;
 };
 
