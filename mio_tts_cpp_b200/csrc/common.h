@@ -94,6 +94,7 @@ struct gemm_args {
     const float * bias;
     const float * res; int ldr;          // fp32 residual: nullptr or == out (read through map_out)
     int red_add;                         // residual added by the L2 (TMA reduce-add store) instead of being read back: set by gemm_launch
+    int split_from, split_shift;         // tiles >= split_from (the partial last wave) are cut into 1 << split_shift column sub-tiles: set by gemm_launch
     const float * gate; int gate_ld;     // gate[utt * gate_ld + n]  (gate_ld 0: one per-column scale for all rows)
     const int * row_utt;                 // row -> utterance (needed with gate_ld != 0)
     const int * row_pos;                 // row -> position in utterance (needed with rope)

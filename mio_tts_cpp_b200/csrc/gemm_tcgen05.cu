@@ -42,7 +42,7 @@ namespace {
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;      // 16-bit elements -> 128-byte rows = one SWIZZLE_128B atom
 constexpr int UMMA_K = 16;
-constexpr int B_BOX_ROWS = 128;  // rows of W per TMA box (a BLOCK_N=256 single-CTA stage takes two boxes)
+constexpr int B_BOX_ROWS = 32;   // rows of W per TMA box: the narrowest split-tail sub-tile (BLOCK_N / 4) of a CTA pair takes one
 constexpr uint32_t PEER_BIT_MASK = 0xFEFFFFFFu;   // clears the CTA-pair rank bit of a shared::cluster address
 constexpr int EPI_NBUF = 3;      // output boxes per epilogue warp (residual prefetch distance = 2 chunks)
 
@@ -406,6 +406,18 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
     const int num_tiles = num_m_tiles * num_n_tiles;
     const int k_blocks = (a.K + BLOCK_K - 1) / BLOCK_K;
     const int k_iters = k_blocks * a.taps;
+    // Work items: tiles [0, split_from) whole; the tiles of the last, partial wave are cut along N into
+    // (1 << split_shift) sub-tiles of BN >> split_shift columns so that the tail occupies more CTA pairs.  The K order of
+    // every output element is unchanged, so results do not depend on the split.
+    const int split_from = a.split_from, split_shift = a.split_shift;
+    const int num_items = split_from + ((num_tiles - split_from) << split_shift);
+    auto item_tile = [&](int w) { return w < split_from ? w : split_from + ((w - split_from) >> split_shift); };
+    auto item_width = [&](int w) { return w < split_from ? BN : (BN >> split_shift); };
+    auto item_n0 = [&](int w) {   // first column of the item
+        const int t = item_tile(w);
+        return (t % num_n_tiles) * BN + (w < split_from ? 0 : ((w - split_from) & ((1 << split_shift) - 1)) * (BN >> split_shift));
+    };
+    auto item_m0 = [&](int w) { return (item_tile(w) / num_n_tiles) * TILE_M; };
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < C::STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
@@ -436,9 +448,12 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
         // ===== TMA producer (every CTA stages its own A rows and its share of the W tile) =====
         if (lane == 0) {
             uint32_t kit = 0;
-            for (int t = unit; t < num_tiles; t += n_units) {
-                const int m0 = (t / num_n_tiles) * TILE_M + cta_rank * BLOCK_M;
-                const int n0 = (t % num_n_tiles) * BN + cta_rank * C::B_ROWS;
+            for (int t = unit; t < num_items; t += n_units) {
+                const int b_rows = item_width(t) / NCTA;               // W rows this CTA stages for the item
+                const int n_boxes = b_rows / B_BOX_ROWS;
+                const uint32_t stage_tx = C::A_BYTES + b_rows * BLOCK_K * 2;
+                const int m0 = item_m0(t) + cta_rank * BLOCK_M;
+                const int n0 = item_n0(t) + cta_rank * b_rows;
                 for (int tap = 0; tap < a.taps; ++tap) {
                     const int arow = m0 + a.tap_row0 + (tap >> a.tap_shift);
                     const int acol = a.a_col0 + (tap & ((1 << a.tap_shift) - 1)) * a.K;
@@ -447,17 +462,15 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
                         mbar_wait(empty_bar(s), ((kit / C::STAGES) & 1) ^ 1);
                         const uint32_t sa = smem_base + s * C::STAGE_BYTES;
                         if constexpr (NCTA == 1) {
-                            mbar_expect_tx(full_bar(s), C::STAGE_BYTES);
+                            mbar_expect_tx(full_bar(s), stage_tx);
                             tma_load_2d(sa, &a.map_a, full_bar(s), acol + kb * BLOCK_K, arow);
-#pragma unroll
-                            for (int bx = 0; bx < C::B_ROWS / B_BOX_ROWS; ++bx)
+                            for (int bx = 0; bx < n_boxes; ++bx)
                                 tma_load_2d(sa + C::A_BYTES + bx * (B_BOX_ROWS * BLOCK_K * 2), &a.map_b, full_bar(s),
                                             tap * a.K + kb * BLOCK_K, n0 + bx * B_BOX_ROWS);
                         } else {
-                            if (cta_rank == 0) mbar_expect_tx(full_bar(s), 2 * C::STAGE_BYTES);   // both CTAs' bytes
+                            if (cta_rank == 0) mbar_expect_tx(full_bar(s), 2 * stage_tx);   // both CTAs' bytes
                             tma_load_2d_pair(sa, &a.map_a, full_bar(s), acol + kb * BLOCK_K, arow);
-#pragma unroll
-                            for (int bx = 0; bx < C::B_ROWS / B_BOX_ROWS; ++bx)
+                            for (int bx = 0; bx < n_boxes; ++bx)
                                 tma_load_2d_pair(sa + C::A_BYTES + bx * (B_BOX_ROWS * BLOCK_K * 2), &a.map_b, full_bar(s),
                                                  tap * a.K + kb * BLOCK_K, n0 + bx * B_BOX_ROWS);
                         }
@@ -470,10 +483,11 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
         if (lane == 0 && cta_rank == 0) {
             // instruction descriptor (cute::UMMA::InstrDescriptor): c=f32 [4,6), a/b format [7,10)/[10,13),
             // K-major a/b (bits 15,16 = 0), N>>3 [17,23), M>>4 [24,29); M counts the rows of the whole pair
-            const uint32_t idesc = (1u << 4) | ((uint32_t) a.dtype << 7) | ((uint32_t) a.dtype << 10) |
-                                   ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (TILE_M >> 4) << 24);
+            const uint32_t idesc0 = (1u << 4) | ((uint32_t) a.dtype << 7) | ((uint32_t) a.dtype << 10) |
+                                    ((uint32_t) (TILE_M >> 4) << 24);
             uint32_t kit = 0, it = 0;
-            for (int t = unit; t < num_tiles; t += n_units, ++it) {
+            for (int t = unit; t < num_items; t += n_units, ++it) {
+                const uint32_t idesc = idesc0 | ((uint32_t) (item_width(t) >> 3) << 17);
                 const int acc = it & 1;
                 mbar_wait(tempty_bar(acc), ((it >> 1) & 1) ^ 1);
                 tcgen05_fence_after();
@@ -498,7 +512,6 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
     } else {
         // ===== epilogue warps (each CTA drains the accumulator of its own 128 rows) =====
         using E = epi_cfg<EPI>;
-        constexpr int CPT = BN / E::CW;              // chunks per (tile, lane quadrant)
         const int quad = warp & 3;                   // TMEM lane quadrant this warp may access
         const int ew = warp - 2;                     // epilogue warp index; column group = ew / 4
         const int cgrp = ew >> 2;
@@ -510,19 +523,19 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
         const bool red_add = EPI == EPI_STORE32 && a.res != nullptr && a.red_add != 0;
         const bool has_res = EPI == EPI_STORE32 && a.res != nullptr && !red_add;
 
-        auto tile_row0 = [&](int t) { return (t / num_n_tiles) * TILE_M + cta_rank * BLOCK_M + quad * 32; };
-        auto chunk_ok = [&](int t, int c) {
-            return c < CPT && (t % num_n_tiles) * BN + c * E::CW < a.N && tile_row0(t) < a.M;
+        auto tile_row0 = [&](int t) { return item_m0(t) + cta_rank * BLOCK_M + quad * 32; };
+        auto chunk_ok = [&](int t, int c) {   // chunk c (of E::CW accumulator columns) of item t holds output
+            return c * E::CW < item_width(t) && item_n0(t) + c * E::CW < a.N && tile_row0(t) < a.M;
         };
         // residual prefetch cursor: walks this warp's chunks in processing order, across tiles
         int pf_t = unit, pf_c = cgrp;
         uint32_t n_ld = 0;
-        auto pf_seek = [&]() { while (pf_t < num_tiles && !chunk_ok(pf_t, pf_c)) { pf_t += n_units; pf_c = cgrp; } };
+        auto pf_seek = [&]() { while (pf_t < num_items && !chunk_ok(pf_t, pf_c)) { pf_t += n_units; pf_c = cgrp; } };
         auto pf_issue = [&]() {   // lane 0: TMA-load the residual box of the cursor's chunk, advance the cursor
-            if (pf_t >= num_tiles) return;
+            if (pf_t >= num_items) return;
             const int b = n_ld % EPI_NBUF;
             mbar_expect_tx(rbar(b), E::BUF_BYTES);
-            tma_load_2d(ebuf + b * E::BUF_BYTES, &a.map_out, rbar(b), (pf_t % num_n_tiles) * BN + pf_c * E::CW, tile_row0(pf_t));
+            tma_load_2d(ebuf + b * E::BUF_BYTES, &a.map_out, rbar(b), item_n0(pf_t) + pf_c * E::CW, tile_row0(pf_t));
             ++n_ld;
             pf_c += EW;
             pf_seek();
@@ -535,8 +548,8 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
         __syncwarp();
 
         uint32_t it = 0, nch = 0;                    // tiles / chunks processed by this warp
-        for (int t = unit; t < num_tiles; t += n_units, ++it) {
-            const int n0 = (t % num_n_tiles) * BN;
+        for (int t = unit; t < num_items; t += n_units, ++it) {
+            const int n0 = item_n0(t);
             const int acc = it & 1;
             const int row0 = tile_row0(t);
             // per-row operands of this tile: the AdaLN gate vector of the row's utterance (STORE32), or the rope-table
@@ -675,7 +688,26 @@ encode_tiled_fn get_encode_fn() {
     return fn;
 }
 
-template <int BN, int EPI, int EW, int NCTA> void launch_t(const gemm_args & a, int num_sms, cudaStream_t st) {
+// Split of the partial last wave: R = tiles % units tiles would keep R of the `units` CTA (pairs) busy for a whole tile
+// time.  Cutting each of them into s column sub-tiles costs about (0.25 + 0.75 / s) of a tile time per pass (the A rows
+// are staged again by every sub-tile; only W and the MMAs shrink), ceil(R * s / units) passes.
+int tail_split_shift(int tiles, int units, int bn, int ncta) {
+    static const int mode = [] { const char * e = std::getenv("MIO_TTS_B200_GEMM_SPLIT"); return e ? std::atoi(e) : -1; }();
+    const int r = tiles % units;
+    if (r == 0 || mode == 0) return 0;
+    int best = 0;
+    float best_cost = 1.0f;
+    for (int sh = 1; sh <= 2; ++sh) {
+        const int s = 1 << sh;
+        if ((bn >> sh) / ncta < B_BOX_ROWS || (bn >> sh) < 64) break;
+        const float cost = (float) ((r * s + units - 1) / units) * (0.25f + 0.75f / (float) s);
+        if (cost < best_cost - 0.05f) { best_cost = cost; best = sh; }
+    }
+    if (mode > 0 && mode <= 2) best = ((bn >> mode) / ncta >= B_BOX_ROWS && (bn >> mode) >= 64) ? mode : 0;   // forced (tests)
+    return best;
+}
+
+template <int BN, int EPI, int EW, int NCTA> void launch_t(const gemm_args & a0, int num_sms, cudaStream_t st) {
     using C = tile_cfg<BN, EPI, EW, NCTA>;
     static bool configured[64] = {false};   // per-device function attribute
     int dev = 0;
@@ -685,11 +717,15 @@ template <int BN, int EPI, int EW, int NCTA> void launch_t(const gemm_args & a, 
                                       C::SMEM_BYTES));
         configured[dev & 63] = true;
     }
-    const int tiles = ((a.M + BLOCK_M * NCTA - 1) / (BLOCK_M * NCTA)) * ((a.N + BN - 1) / BN);
+    const int tiles = ((a0.M + BLOCK_M * NCTA - 1) / (BLOCK_M * NCTA)) * ((a0.N + BN - 1) / BN);
     const int units = num_sms / NCTA;
+    gemm_args a = a0;
+    a.split_shift = tail_split_shift(tiles, units, BN, NCTA);
+    a.split_from = a.split_shift ? tiles - tiles % units : tiles;
+    const int items = a.split_from + ((tiles - a.split_from) << a.split_shift);
     cudaLaunchConfig_t cfg;
     std::memset(&cfg, 0, sizeof(cfg));
-    cfg.gridDim = dim3((unsigned) (NCTA * (tiles < units ? tiles : units)));
+    cfg.gridDim = dim3((unsigned) (NCTA * (items < units ? items : units)));
     cfg.blockDim = dim3(C::THREADS);
     cfg.dynamicSmemBytes = C::SMEM_BYTES;
     cfg.stream = st;

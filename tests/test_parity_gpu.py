@@ -236,3 +236,32 @@ def test_f16_linear_mode_is_closer(gguf_paths, emb):
     assert out.returncode == 0, out.stderr[-2000:]
     line = [ln for ln in out.stdout.splitlines() if ln.startswith("SNR")][-1].split()
     assert float(line[1]) >= 50.0 and float(line[2]) >= 40.0, line
+
+
+def test_gemm_tail_split_is_bit_invariant(gguf_paths, emb):
+    """The GEMM cuts the tiles of its partial last wave into 2 or 4 column sub-tiles (MIO_TTS_B200_GEMM_SPLIT: 0 off,
+    1 / 2 forced shift, unset = cost model).  The K order of every output element is unchanged, so spectrogram and
+    waveform must be bit-identical in every mode.  Subprocesses: the mode is read once per process."""
+    path = gguf_paths("default")[0]
+    code = (
+        "import sys, hashlib, numpy as np; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "from mio_tts_cpp_b200 import MioTTS\n"
+        "emb = np.load(%r); rng = np.random.default_rng(5)\n"
+        "m = MioTTS(%r); h = hashlib.sha256()\n"
+        "for T in (1, 37, 400):\n"
+        "    c = rng.integers(0, 12800, T).astype(np.int32)\n"
+        "    h.update(m.decode_spec(c, emb).tobytes()); h.update(m.synthesize(c, emb)[0].tobytes())\n"
+        "codes = [rng.integers(0, 12800, int(t)).astype(np.int32) for t in rng.integers(50, 400, 24)]\n"
+        "for a in m.synthesize_batch(codes, [emb] * len(codes))[0]: h.update(np.asarray(a).tobytes())\n"
+        "print('HASH', h.hexdigest())\n"
+    ) % (ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "tests", "golden", "en_female_emb.npy"), path)
+    hashes = {}
+    for mode in ("0", "1", "2", None):
+        env = dict(os.environ)
+        env.pop("MIO_TTS_B200_GEMM_SPLIT", None)
+        if mode is not None:
+            env["MIO_TTS_B200_GEMM_SPLIT"] = mode
+        out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+        assert out.returncode == 0, out.stderr[-2000:]
+        hashes[mode] = [ln for ln in out.stdout.splitlines() if ln.startswith("HASH")][-1].split()[1]
+    assert len(set(hashes.values())) == 1, hashes
