@@ -5,6 +5,9 @@
 
 #include "batcher.h"
 #include "engine.h"
+
+#include <atomic>
+#include <chrono>
 #include "gguf_io.h"
 #include "refenc.h"
 
@@ -26,6 +29,9 @@ using namespace mio;
 struct mio_tts_context {
     std::shared_ptr<model> mdl;
     std::unique_ptr<engine> eng;
+    std::unique_ptr<engine> eng2;       // second stream + workspace for large single-caller batches (created on first use)
+    std::mutex eng2_mtx;
+    uint64_t last_h2d = 0;              // bytes uploaded by the last synthesize call on this context (both halves)
     std::shared_ptr<refmodel> ref;      // WavLM + global-encoder weights (reference-audio path), shared by clones
     std::unique_ptr<refenc> renc;       // per-context stream + workspace of that path
     std::shared_ptr<batcher> bat;       // micro-batcher shared with the clones (null: calls decode on this context's engine)
@@ -338,6 +344,7 @@ bool mio_tts_context_set_backend_device(struct mio_tts_context * ctx, const char
         auto r = load_refmodel(ctx->vocoder_path, ctx->wavlm_path, dev, m->hp.decoder_adanorm_dim, load_err);
         if (!r) throw std::runtime_error("wavlm backend setup failed: " + load_err);
         ctx->eng.reset();
+        ctx->eng2.reset();
         ctx->renc.reset();
         ctx->mdl = m;
         ctx->ref = r;
@@ -622,6 +629,16 @@ bool mio_tts_embedding_save_gguf(const char * path, const float * embedding, siz
 
 void mio_tts_embedding_free(float * embedding) { std::free(embedding); }
 
+// MIO_TTS_B200_PIPELINE_CODES: smallest batch (in codes) that is decoded as two pipelined halves; 0 = never
+static size_t pipeline_min_codes() {
+    static const size_t v = [] {
+        const char * e = std::getenv("MIO_TTS_B200_PIPELINE_CODES");
+        const long long x = e ? std::atoll(e) : 20000;
+        return x <= 0 ? (size_t) -1 : (size_t) x;
+    }();
+    return v;
+}
+
 // shared body of the batch entry points: fp32 waveforms (wav16 = false) or RIFF/WAVE 16-bit buffers (wav16 = true)
 static bool synthesize_batch_any(struct mio_tts_context * ctx, const int32_t * const * codes, const size_t * n_codes,
                                  const float * const * embedding, size_t n_embedding, size_t batch, bool wav16, void ** out,
@@ -646,7 +663,34 @@ static bool synthesize_batch_any(struct mio_tts_context * ctx, const int32_t * c
     if (batch == 1 && ctx->bat) {
         ctx->bat->submit(reqs[0]);             // coalesced with whatever the other slots have queued
         if (!reqs[0].ok) { set_err(err, err_size, reqs[0].err); return false; }
-    } else if (!guarded(err, err_size, [&] { decode_batch(*ctx->eng, rp.data(), batch); })) {
+    } else if (!guarded(err, err_size, [&] {
+                   // A batch large enough that each half still fills the GPU (>= ~10 k codes per half) runs as two
+                   // pipelined halves: device -> host copies of the first under the kernels of the second.
+                   size_t total = 0;
+                   for (size_t u = 0; u < batch; ++u) total += n_codes[u];
+                   // Only for a lone caller: with other batch calls in flight (server slots, each on its own clone) the
+                   // copies of one call already hide under the kernels of another, and four interleaved streams cost 3 %.
+                   // "Lone" = no two batch calls overlapped during the last 200 ms (slots that run in lockstep leave short
+                   // windows with nothing in flight, so the instantaneous count alone is not enough).
+                   static std::atomic<int> in_flight{0};
+                   static std::atomic<long long> last_overlap_ns{-(1ll << 62)};
+                   struct flight { int n; flight() : n(++in_flight) {} ~flight() { --in_flight; } } fl;
+                   const long long now_ns = std::chrono::duration_cast<std::chrono::nanoseconds>(
+                                                std::chrono::steady_clock::now().time_since_epoch()).count();
+                   if (fl.n >= 2) last_overlap_ns.store(now_ns);
+                   const bool lone = fl.n == 1 && now_ns - last_overlap_ns.load() > 200000000ll;
+                   if (batch >= 2 && total >= pipeline_min_codes() && lone) {
+                       {
+                           std::lock_guard<std::mutex> lk(ctx->eng2_mtx);
+                           if (!ctx->eng2) ctx->eng2.reset(new engine(ctx->mdl));
+                       }
+                       decode_batch_pipelined(*ctx->eng, *ctx->eng2, rp.data(), batch);
+                       ctx->last_h2d = ctx->eng->h2d_bytes() + ctx->eng2->h2d_bytes();
+                   } else {
+                       decode_batch(*ctx->eng, rp.data(), batch);
+                       ctx->last_h2d = ctx->eng->h2d_bytes();
+                   }
+               })) {
         return false;
     }
     for (size_t u = 0; u < batch; ++u) { out[u] = reqs[u].out; n_out[u] = wav16 ? 44 + 2 * reqs[u].n_samples : reqs[u].n_samples; }
@@ -1018,7 +1062,7 @@ uint64_t mio_tts_b200_weight_bytes(struct mio_tts_context * ctx) {
 }
 
 uint64_t mio_tts_b200_last_h2d_bytes(struct mio_tts_context * ctx) {
-    return (ctx == nullptr || !ctx->eng) ? 0 : (uint64_t) ctx->eng->h2d_bytes();
+    return (ctx == nullptr || !ctx->eng) ? 0 : (ctx->last_h2d ? ctx->last_h2d : (uint64_t) ctx->eng->h2d_bytes());
 }
 
 } // extern "C"

@@ -56,6 +56,67 @@ void decode_batch(engine & E, decode_request * const * reqs, size_t batch, const
     for (size_t u = 0; u < batch; ++u) { reqs[u]->out = bufs[u]; reqs[u]->n_samples = E.audio_len(u); reqs[u]->ok = true; }
 }
 
+// One large batch from ONE caller, as two halves on two engines (streams + workspaces): the second half's kernels are
+// ordered behind the first half's by an event, and the first half's device -> host copies run on its own stream under
+// them.  The halves are cut at the utterance where half of the codes is reached; no kernel mixes utterances, so every
+// waveform is bit-identical to the single-batch path.
+void decode_batch_pipelined(engine & E1, engine & E2, decode_request * const * reqs, size_t batch) {
+    if (batch < 2) { decode_batch(E1, reqs, batch); return; }
+    size_t total = 0, acc = 0, cut = batch / 2;
+    for (size_t u = 0; u < batch; ++u) total += reqs[u]->n_codes;
+    for (size_t u = 0; u < batch; ++u) { acc += reqs[u]->n_codes; if (2 * acc >= total) { cut = u + 1; break; } }
+    cut = std::min(std::max<size_t>(cut, 1), batch - 1);
+    std::vector<const int32_t *> codes(batch);
+    std::vector<size_t> n(batch);
+    std::vector<const float *> embs(batch);
+    const bool has_emb = reqs[0]->emb != nullptr && reqs[0]->n_emb > 0;
+    const bool wav16 = reqs[0]->wav16;
+    for (size_t u = 0; u < batch; ++u) { codes[u] = reqs[u]->codes; n[u] = reqs[u]->n_codes; embs[u] = reqs[u]->emb; }
+    std::vector<void *> bufs(batch, nullptr);
+    std::vector<size_t> ns(batch, 0);
+    std::lock(E1.mtx, E2.mtx);
+    std::lock_guard<std::mutex> lk1(E1.mtx, std::adopt_lock), lk2(E2.mtx, std::adopt_lock);
+    engine * eng[2] = {&E1, &E2};
+    const size_t lo[2] = {0, cut}, hi[2] = {cut, batch};
+    cudaEvent_t ev = nullptr;
+    try {
+        MIO_CUDA(cudaSetDevice(E1.mdl->device));
+        MIO_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        for (int h = 0; h < 2; ++h) {
+            engine & E = *eng[h];
+            E.out_pcm16 = wav16;
+            E.prepare(codes.data() + lo[h], n.data() + lo[h], has_emb ? embs.data() + lo[h] : nullptr, has_emb ? reqs[0]->n_emb : 0,
+                      hi[h] - lo[h]);
+            if (h == 1) MIO_CUDA(cudaStreamWaitEvent(E.stream(), ev, 0));     // kernels of half 2 behind the kernels of half 1
+            E.run(true);
+            if (h == 0) MIO_CUDA(cudaEventRecord(ev, E.stream()));            // ... but not behind its copies
+            for (size_t u = lo[h]; u < hi[h]; ++u) {
+                ns[u] = E.audio_len(u - lo[h]);
+                bufs[u] = wav16 ? (void *) result_alloc((44 + 2 * ns[u] + 3) / 4) : (void *) result_alloc(ns[u]);
+                if (bufs[u] == nullptr) throw std::runtime_error("failed to allocate output audio");
+                if (wav16) {
+                    wav16_header((uint8_t *) bufs[u], (uint32_t) E.mdl->hp.sample_rate, (uint32_t) (2 * ns[u]));
+                    E.fetch_pcm16(u - lo[h], (int16_t *) ((uint8_t *) bufs[u] + 44));
+                } else {
+                    E.fetch_audio(u - lo[h], (float *) bufs[u]);
+                }
+            }
+        }
+        E1.sync();
+        E2.sync();
+        E1.out_pcm16 = E2.out_pcm16 = false;
+        cudaEventDestroy(ev);
+    } catch (...) {
+        E1.out_pcm16 = E2.out_pcm16 = false;
+        try { E1.sync(); } catch (...) {}
+        try { E2.sync(); } catch (...) {}
+        if (ev) cudaEventDestroy(ev);
+        for (void * p : bufs) if (p && !result_free(p)) std::free(p);
+        throw;
+    }
+    for (size_t u = 0; u < batch; ++u) { reqs[u]->out = bufs[u]; reqs[u]->n_samples = ns[u]; reqs[u]->ok = true; }
+}
+
 batcher::batcher(std::shared_ptr<model> m, int max_batch_, int max_wait_us_, int workers_)
     : max_batch(std::max(1, max_batch_)), max_wait_us(std::max(0, max_wait_us_)), workers(std::min(8, std::max(1, workers_))),
       mdl(std::move(m)) {

@@ -34,6 +34,9 @@ struct decode_request {
 // One batch on one engine: prepare -> run -> pinned result buffers.  Throws std::runtime_error (nothing is leaked).
 // kernels_done (optional) is called once the batch's kernels have finished, before the device -> host copies start.
 void decode_batch(engine & E, decode_request * const * reqs, size_t batch, const std::function<void()> & kernels_done = nullptr);
+// The same for one large batch of a single caller, as two halves on two engines so that the first half's device -> host
+// copies hide under the second half's kernels (bit-identical results; see batcher.cu)
+void decode_batch_pipelined(engine & E1, engine & E2, decode_request * const * reqs, size_t batch);
 void wav16_header(uint8_t * p, uint32_t sample_rate, uint32_t pcm_bytes);   // tts-mio-server.cpp:2013-2034, lib.cpp:34-48
 
 struct batcher_stats { uint64_t requests = 0, batches = 0, largest = 0, retried_single = 0; };

@@ -265,3 +265,33 @@ def test_gemm_tail_split_is_bit_invariant(gguf_paths, emb):
         assert out.returncode == 0, out.stderr[-2000:]
         hashes[mode] = [ln for ln in out.stdout.splitlines() if ln.startswith("HASH")][-1].split()[1]
     assert len(set(hashes.values())) == 1, hashes
+
+
+def test_pipelined_halves_match_single_calls(ctxs, emb):
+    """A batch of >= 20 000 codes from one caller is decoded as two pipelined halves on two engines (device -> host
+    copies of the first under the kernels of the second: batcher.cu decode_batch_pipelined).  Ragged lengths so the cut
+    is not at batch / 2; every waveform must be bit-identical to its own mio_tts_synthesize call, fp32 and WAV16, and an
+    error in the second half must fail the whole call and leave the context usable."""
+    from mio_tts_cpp_b200 import MioTtsError
+
+    m = ctxs("default")
+    rng = np.random.default_rng(23)
+    lens = [int(x) for x in rng.integers(200, 700, 56)]
+    assert sum(lens) >= 20000
+    codes = [rng.integers(0, 12800, n).astype(np.int32) for n in lens]
+    embs = [emb * (1.0 + 0.01 * i) for i in range(len(lens))]
+    a, sr = m.synthesize_batch(codes, embs)
+    assert sr == 24000 and [x.size for x in a] == [n * m.samples_per_token() for n in lens]
+    for i in (0, 1, 20, 27, 28, 29, 40, 55):
+        single, _ = m.synthesize(codes[i], embs[i])
+        assert single.tobytes() == a[i].tobytes(), i
+    wavs = m.synthesize_wav16_batch(codes, embs)
+    for i in (0, 27, 55):
+        one = m.synthesize_wav16_batch([codes[i]], [embs[i]])[0]
+        assert one == wavs[i], i
+    bad = [c.copy() for c in codes]
+    bad[50][3] = 12800
+    with pytest.raises(MioTtsError, match="code id out of range"):
+        m.synthesize_batch(bad, embs)
+    b, _ = m.synthesize_batch(codes, embs)
+    assert all(x.tobytes() == y.tobytes() for x, y in zip(a, b))
