@@ -548,6 +548,11 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
         __syncwarp();
 
         uint32_t it = 0, nch = 0;                    // tiles / chunks processed by this warp
+        // ROPE16: this lane's row position, loaded one item ahead so that its latency never sits in front of a tile
+        int pos_next = 0;
+        if constexpr (EPI == EPI_ROPE16) {
+            if (unit < num_items) { const int r = tile_row0(unit) + lane; pos_next = r < a.M ? __ldg(a.row_pos + r) : 0; }
+        }
         for (int t = unit; t < num_items; t += n_units, ++it) {
             const int n0 = item_n0(t);
             const int acc = it & 1;
@@ -562,7 +567,8 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
                     gate_row = a.gate + (size_t) utt * a.gate_ld;
                 }
             } else if constexpr (EPI == EPI_ROPE16) {
-                const int pos = row0 + lane < a.M ? max(__ldg(a.row_pos + row0 + lane), 0) : 0;
+                const int pos = max(pos_next, 0);
+                if (t + n_units < num_items) { const int r = tile_row0(t + n_units) + lane; pos_next = r < a.M ? __ldg(a.row_pos + r) : 0; }
 #pragma unroll
                 for (int u = 0; u < 8; ++u) {
                     const int p = __shfl_sync(0xffffffffu, pos, (lane >> 3) + 4 * u);
@@ -570,6 +576,20 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
                 }
             }
             const uint32_t taddr = tmem_base + ((uint32_t) (quad * 32) << 16) + acc * BN;
+            // RoPE: the (cos,sin) rows of a chunk are fetched one chunk ahead (the first before the accumulator wait),
+            // so their L2 latency hides behind the previous chunk's math instead of stalling every chunk
+            float4 cs[EPI == EPI_ROPE16 ? 8 : 1];
+            auto rope_fetch = [&](int c) {
+                if constexpr (EPI == EPI_ROPE16) {
+                    const int n = n0 + c * E::CW;
+                    if (chunk_ok(t, c) && n < a.rope_cols) {
+                        const int p0 = (n % a.head_dim) >> 2;    // first pair of the chunk, in float4 (2-pair) units
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) cs[u] = __ldg(rope_row[u] + p0);
+                    }
+                }
+            };
+            rope_fetch(cgrp);
             mbar_wait(tfull_bar(acc), (it >> 1) & 1);
             tcgen05_fence_after();
 #pragma unroll 1
@@ -581,20 +601,15 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
                 if constexpr (EPI == EPI_ROPE16) {
                     // this chunk's (cos,sin) rows: coalesced global reads, transposed through the staging tile
                     const bool rotate = n < a.rope_cols;
+                    tmem_ld_32x32b_x32(taddr + c * 32, raw);
                     if (rotate) {
-                        const int p0 = (n % a.head_dim) >> 2;    // first pair of the chunk, in float4 (2-pair) units
-                        float4 cs[8];
-#pragma unroll
-                        for (int u = 0; u < 8; ++u) cs[u] = __ldg(rope_row[u] + p0);
-                        tmem_ld_32x32b_x32(taddr + c * 32, raw);
 #pragma unroll
                         for (int u = 0; u < 8; ++u) {
                             const int rr = (lane >> 3) + 4 * u;
                             sts128(rope_st + rr * 128 + ((uint32_t) ((lane & 7) ^ (rr & 7)) << 4), cs[u]);
                         }
-                    } else {
-                        tmem_ld_32x32b_x32(taddr + c * 32, raw);
                     }
+                    rope_fetch(c + EW);
                     if (lane == 0) bulk_wait_read<EPI_NBUF - 1>();
                     __syncwarp();
                     tmem_ld_wait();
