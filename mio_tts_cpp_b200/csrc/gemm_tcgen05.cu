@@ -241,31 +241,23 @@ __device__ __forceinline__ float act_apply(float x, int act) {
 }
 
 // fp32 box: out = act(acc + bias) * gate + residual, residual read from / result written to the same box slot.
-// BIAS/GATE/RES are compile-time so an absent term costs no issue slots; GUARD handles the last, partial N tile.
-template <bool BIAS, bool GATE, bool RES, bool GUARD>
-__device__ __forceinline__ void chunk_store32(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, int lane, int n,
-                                              const float * gate_row) {
+// BIAS/GATE/RES are compile-time so an absent term costs no issue slots.  The bias / gate values of the chunk (bv, gv)
+// were fetched by the caller one chunk ahead (zeros past N: those columns are clipped by the TMA store).
+template <bool BIAS, bool GATE, bool RES>
+__device__ __forceinline__ void chunk_store32(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, int lane,
+                                              const float4 (&bv)[8], const float4 (&gv)[8]) {
     const uint32_t row = buf + lane * 128;
     const uint32_t sw = (uint32_t) (lane & 7) << 4;
-    const float4 * bias4 = reinterpret_cast<const float4 *>(a.bias + n);
-    const float4 * gate4 = reinterpret_cast<const float4 *>(gate_row + n);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         const uint32_t addr = row + (((uint32_t) j << 4) ^ sw);
         float4 o = make_float4(__uint_as_float(raw[4 * j]), __uint_as_float(raw[4 * j + 1]), __uint_as_float(raw[4 * j + 2]),
                                __uint_as_float(raw[4 * j + 3]));
-        const bool in = !GUARD || n + 4 * j < a.N;   // columns past N are clipped by the TMA store; do not read past the vectors
-        if (BIAS && in) {
-            const float4 b = __ldg(bias4 + j);
-            o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
-        }
+        if (BIAS) { o.x += bv[j].x; o.y += bv[j].y; o.z += bv[j].z; o.w += bv[j].w; }
         if (a.act != 0) {   // warp-uniform
             o.x = act_apply(o.x, a.act); o.y = act_apply(o.y, a.act); o.z = act_apply(o.z, a.act); o.w = act_apply(o.w, a.act);
         }
-        if (GATE && in) {
-            const float4 g = __ldg(gate4 + j);
-            o.x *= g.x; o.y *= g.y; o.z *= g.z; o.w *= g.w;
-        }
+        if (GATE) { o.x *= gv[j].x; o.y *= gv[j].y; o.z *= gv[j].z; o.w *= gv[j].w; }
         if (RES) {
             const float4 q = lds128(addr);
             o.x += q.x; o.y += q.y; o.z += q.z; o.w += q.w;
@@ -274,29 +266,22 @@ __device__ __forceinline__ void chunk_store32(const gemm_args & a, const uint32_
     }
 }
 
-template <bool GUARD>
-__device__ __forceinline__ void chunk_store32_pick(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, int lane, int n,
-                                                   const float * gate_row, bool has_res) {
-    if (a.gate) {
-        if (has_res) { if (a.bias) chunk_store32<true, true, true, GUARD>(a, raw, buf, lane, n, gate_row);
-                       else chunk_store32<false, true, true, GUARD>(a, raw, buf, lane, n, gate_row); }
-        else { if (a.bias) chunk_store32<true, true, false, GUARD>(a, raw, buf, lane, n, gate_row);
-               else chunk_store32<false, true, false, GUARD>(a, raw, buf, lane, n, gate_row); }
-    } else if (has_res) {
-        if (a.bias) chunk_store32<true, false, true, GUARD>(a, raw, buf, lane, n, gate_row);
-        else chunk_store32<false, false, true, GUARD>(a, raw, buf, lane, n, gate_row);
-    } else {
-        if (a.bias) chunk_store32<true, false, false, GUARD>(a, raw, buf, lane, n, gate_row);
-        else chunk_store32<false, false, false, GUARD>(a, raw, buf, lane, n, gate_row);
-    }
-}
-
 // warp-uniform dispatch to the term combinations in use; has_res: the residual sits in the box and is added here
 // (false in reduce-add mode, where the box carries the new term alone)
-__device__ __forceinline__ void chunk_store32_any(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, int lane, int n,
-                                                  const float * gate_row, bool has_res) {
-    if (n + 32 <= a.N) chunk_store32_pick<false>(a, raw, buf, lane, n, gate_row, has_res);
-    else chunk_store32_pick<true>(a, raw, buf, lane, n, gate_row, has_res);
+__device__ __forceinline__ void chunk_store32_any(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, int lane,
+                                                  const float4 (&bv)[8], const float4 (&gv)[8], bool has_res) {
+    if (a.gate) {
+        if (has_res) { if (a.bias) chunk_store32<true, true, true>(a, raw, buf, lane, bv, gv);
+                       else chunk_store32<false, true, true>(a, raw, buf, lane, bv, gv); }
+        else { if (a.bias) chunk_store32<true, true, false>(a, raw, buf, lane, bv, gv);
+               else chunk_store32<false, true, false>(a, raw, buf, lane, bv, gv); }
+    } else if (has_res) {
+        if (a.bias) chunk_store32<true, false, true>(a, raw, buf, lane, bv, gv);
+        else chunk_store32<false, false, true>(a, raw, buf, lane, bv, gv);
+    } else {
+        if (a.bias) chunk_store32<true, false, false>(a, raw, buf, lane, bv, gv);
+        else chunk_store32<false, false, false>(a, raw, buf, lane, bv, gv);
+    }
 }
 
 template <bool BF16> __device__ __forceinline__ uint32_t pack16t(float a, float b) {
@@ -553,6 +538,12 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
         if constexpr (EPI == EPI_ROPE16) {
             if (unit < num_items) { const int r = tile_row0(unit) + lane; pos_next = r < a.M ? __ldg(a.row_pos + r) : 0; }
         }
+        // STORE32 with a per-utterance gate: likewise this lane's row -> utterance index
+        auto utt_of = [&](int w) {
+            const int r = tile_row0(w) + lane;
+            return (a.gate != nullptr && a.row_utt != nullptr && w < num_items && r < a.M) ? __ldg(a.row_utt + r) : 0;
+        };
+        int utt_next = EPI == EPI_STORE32 ? utt_of(unit) : 0;
         for (int t = unit; t < num_items; t += n_units, ++it) {
             const int n0 = item_n0(t);
             const int acc = it & 1;
@@ -562,10 +553,8 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
             const float * gate_row = nullptr;
             const float4 * rope_row[EPI == EPI_ROPE16 ? 8 : 1];
             if constexpr (EPI == EPI_STORE32) {
-                if (a.gate) {
-                    const int utt = (a.row_utt != nullptr && row0 + lane < a.M) ? max(__ldg(a.row_utt + row0 + lane), 0) : 0;
-                    gate_row = a.gate + (size_t) utt * a.gate_ld;
-                }
+                if (a.gate) gate_row = a.gate + (size_t) max(utt_next, 0) * a.gate_ld;
+                utt_next = utt_of(t + n_units);
             } else if constexpr (EPI == EPI_ROPE16) {
                 const int pos = max(pos_next, 0);
                 if (t + n_units < num_items) { const int r = tile_row0(t + n_units) + lane; pos_next = r < a.M ? __ldg(a.row_pos + r) : 0; }
@@ -590,6 +579,25 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
                 }
             };
             rope_fetch(cgrp);
+            // STORE32: bias and gate values of a chunk, fetched the same way (they were 4-8 serialised L2 round trips
+            // in front of the math of every chunk: 40 % of the epilogue samples of the O-projections)
+            float4 bv[EPI == EPI_STORE32 ? 8 : 1], gv[EPI == EPI_STORE32 ? 8 : 1];
+            auto bg_fetch = [&](int c) {
+                if constexpr (EPI == EPI_STORE32) {
+                    if (!chunk_ok(t, c)) return;
+                    const int n = n0 + c * E::CW;
+                    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (a.bias) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) bv[j] = n + 4 * j < a.N ? __ldg(reinterpret_cast<const float4 *>(a.bias + n) + j) : z;
+                    }
+                    if (gate_row) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) gv[j] = n + 4 * j < a.N ? __ldg(reinterpret_cast<const float4 *>(gate_row + n) + j) : z;
+                    }
+                }
+            };
+            bg_fetch(cgrp);
             mbar_wait(tfull_bar(acc), (it >> 1) & 1);
             tcgen05_fence_after();
 #pragma unroll 1
@@ -642,7 +650,8 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
                     if (has_res) mbar_wait(rbar(b), (nch / EPI_NBUF) & 1);       // residual box landed
                     else { if (lane == 0) bulk_wait_read<EPI_NBUF - 1>(); __syncwarp(); }
                     tmem_ld_wait();
-                    chunk_store32_any(a, raw, buf, lane, n, gate_row, has_res);
+                    chunk_store32_any(a, raw, buf, lane, bv, gv, has_res);
+                    bg_fetch(c + EW);
                 }
                 fence_proxy_async();
                 __syncwarp();
