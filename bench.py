@@ -31,49 +31,116 @@ def baseline_metric():
         return "MioCodec+iSTFT audio-seconds/sec (RTF^-1) per GPU and at 8xB200"
 
 
-def time_cpu_reference(n_utt, n_codes, warmup=0):
+def _cpu_ref_loop(codes, emb, n_threads, warmup, keep=()):
+    """Sequential mio_tts_synthesize calls of the compiled reference on `codes` (first `warmup` untimed).
+    Returns (audio seconds, wall seconds, t_start, t_end, {index: waveform} for the timed indices in `keep`)."""
+    from oracle.refbind import RefLib
+
+    R = RefLib()
+    ctx = R.open_context(U.synth_gguf("default"))
+    devnull, saved = os.open(os.devnull, os.O_WRONLY), os.dup(2)
+    os.dup2(devnull, 2)            # the reference prints a "synth breakdown" line per call on stderr
+    kept = {}
+    try:
+        for i in range(warmup):
+            R.synthesize(ctx, codes[i], emb, n_threads=n_threads)
+        go = float(os.environ.get("MIO_BENCH_CPU_GO", "0"))
+        while time.time() < go:     # packed arrangement: every process starts its timed loop at the same instant
+            time.sleep(0.001)
+        t_start, secs = time.time(), 0.0
+        t0 = time.perf_counter()
+        for i in range(warmup, len(codes)):
+            a, sr = R.synthesize(ctx, codes[i], emb, n_threads=n_threads)
+            secs += a.size / sr
+            if i - warmup in keep:
+                kept[i - warmup] = a
+        dt = time.perf_counter() - t0
+        t_end = time.time()
+    finally:
+        os.dup2(saved, 2)
+        os.close(devnull)
+        os.close(saved)
+    R.close_context(ctx)
+    return secs, dt, t_start, t_end, kept
+
+
+def time_cpu_reference(n_utt, n_codes, warmup=0, n_threads=None, keep=()):
     """The reference's own CPU mio_tts_synthesize (oracle/_ref = the unmodified reference compiled from
-    /root/reference; else the numpy port), `n_utt` sequential utterances with all host threads -- the reference has
-    no batch API.  This is the ONLY place bench.py executes anything under oracle/."""
+    /root/reference; else the numpy port), `n_utt` sequential utterances with `n_threads` (default: all) host threads --
+    the reference has no batch API.  bench.py executes oracle/ only here and in cpu_arrangements below."""
     from oracle.refbind import RefLib, ref_lib_path
 
     emb = U.speaker_embedding()
     codes = U.config2_workload(0, n_utt + warmup, n_codes)
+    if warmup:                      # warm-up utterances come from the END of the list: timed index i = utterance i
+        codes = codes[n_utt:] + codes[:n_utt]
     if ref_lib_path() is not None:
-        R = RefLib()
-        cores = R.hw_threads()
-        ctx = R.open_context(U.synth_gguf("default"))
-        devnull, saved = os.open(os.devnull, os.O_WRONLY), os.dup(2)
-        os.dup2(devnull, 2)            # the reference prints a "synth breakdown" line per call on stderr
-        try:
-            for i in range(warmup):
-                R.synthesize(ctx, codes[i], emb, n_threads=cores)
-            t0, secs = time.perf_counter(), 0.0
-            for i in range(n_utt):
-                a, sr = R.synthesize(ctx, codes[warmup + i], emb, n_threads=cores)
-                secs += a.size / sr
-            dt = time.perf_counter() - t0
-        finally:
-            os.dup2(saved, 2)
-            os.close(devnull)
-            os.close(saved)
-        R.close_context(ctx)
-        return secs / dt, cores, "reference", dt
+        cores = RefLib().hw_threads()
+        secs, dt, _, _, kept = _cpu_ref_loop(codes, emb, n_threads or cores, warmup, keep)
+        return secs / dt, n_threads or cores, "reference", dt, kept
     from oracle import miocodec_np as O
 
     m = O.Model(U.synth_gguf("default"))
-    t0, secs = time.perf_counter(), 0.0
+    t0, secs, kept = time.perf_counter(), 0.0, {}
     for i in range(n_utt):
-        secs += O.synthesize(m, codes[warmup + i], emb).size / m.hp["sample_rate"]
+        a = O.synthesize(m, codes[warmup + i], emb)
+        secs += a.size / m.hp["sample_rate"]
+        if i in keep:
+            kept[i] = a
     dt = time.perf_counter() - t0
-    return secs / dt, 1, "port", dt
+    return secs / dt, 1, "port", dt, kept
+
+
+def cpu_worker_main(argv):
+    """`bench.py --cpu-worker <threads> <n_utt> <first utterance>`: one process of the packed CPU arrangement."""
+    k, n_utt, first = int(argv[0]), int(argv[1]), int(argv[2])
+    codes = U.config2_workload(0, 64, N_CODES)
+    mine = [codes[(first + i) % 64] for i in range(n_utt + 1)]
+    secs, dt, t_start, t_end, _ = _cpu_ref_loop(mine[-1:] + mine[:-1], U.speaker_embedding(), k, 1)
+    print(json.dumps({"secs": secs, "dt": dt, "t_start": t_start, "t_end": t_end}), flush=True)
+
+
+def cpu_arrangements(runs=5):
+    """the reference on this box's host cores in the arrangements a deployment could choose --
+    (a) all hardware threads on one utterance at a time, (b) n_threads = 2 (the CLI / server default), (c) packed:
+    cores / 2 processes x 2 threads, each decoding its own utterances at the same time.  min / median over `runs`
+    runs each; every run is a bounded sample of config 2 (whole utterances of 400 codes)."""
+    import statistics
+    import subprocess
+
+    from oracle.refbind import RefLib, ref_lib_path
+
+    if ref_lib_path() is None:
+        return None
+    cores = RefLib().hw_threads()
+    out = {}
+    for name, k, n_utt in (("all_threads", cores, 4), ("two_threads", 2, 1)):
+        vals = [time_cpu_reference(n_utt, N_CODES, warmup=1 if r == 0 else 0, n_threads=k)[0] for r in range(runs)]
+        out[name] = {"threads": k, "utterances_per_run": n_utt, "runs": runs, "median": statistics.median(vals),
+                     "min": min(vals), "max": max(vals)}
+    procs, k, n_utt = max(1, cores // 2), 2, 2
+    vals = []
+    for r in range(runs):
+        env = dict(os.environ, MIO_BENCH_CPU_GO=str(time.time() + 6.0), OMP_NUM_THREADS=str(k))
+        ps = [subprocess.Popen([sys.executable, os.path.abspath(__file__), "--cpu-worker", str(k), str(n_utt), str(p * n_utt)],
+                               stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, env=env) for p in range(procs)]
+        rows = []
+        for q in ps:
+            o, _ = q.communicate(timeout=600)
+            rows += [json.loads(ln) for ln in o.splitlines() if ln.startswith("{")]
+        if len(rows) == procs:
+            vals.append(sum(x["secs"] for x in rows) / (max(x["t_end"] for x in rows) - min(x["t_start"] for x in rows)))
+    if vals:
+        out["packed"] = {"processes": procs, "threads": k, "utterances_per_process": n_utt, "runs": len(vals),
+                         "median": statistics.median(vals), "min": min(vals), "max": max(vals)}
+    return out
 
 
 def run_reference(args, rank):
     if rank != 0:
         return
     per_step = 2   # utterances per step: a bounded sample of config 2 (the CPU path takes ~1 s per utterance)
-    v, cores, kind, dt = time_cpu_reference(per_step * args.steps, N_CODES, warmup=min(args.warmup, 2))
+    v, cores, kind, dt, _ = time_cpu_reference(per_step * args.steps, N_CODES, warmup=min(args.warmup, 2))
     sample = f"{per_step * args.steps} of the 64 utterances x {N_CODES} codes, sequential mio_tts_synthesize, {cores} threads"
     line = {"impl": "reference", "metric": baseline_metric(), "value": v, "unit": "audio-seconds/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(1, args.steps),
@@ -149,10 +216,22 @@ def run_b200(args, rank, world, local_rank):
     barrier()
     ms = max_over_ranks(ms)
     total_audio = sum_over_ranks(audio_s_per_step)
+    sum_audio_all = total_audio
     value = total_audio / (ms * 1e-3)
 
     # per-launch GEMM timings for the roofline, taken right after the timed region (same clocks and power state)
     profs = [m.profile_resident() for _ in range(3)] if rank == 0 else []
+
+    # ---- sustained leg: >= 2.5 s of back-to-back steps with its own clock record, the like-for-like numerator for the
+    # SUSTAINED bf16 peak of MEASURED_PEAKS.json (taken over seconds under the power cap); the K-step region above is
+    # a fraction of a second and belongs beside the burst peak
+    sus_steps = int(max(args.steps, min(2000, 2500.0 / max(ms, 0.05))))
+    barrier()
+    torch.cuda.synchronize()
+    with U.ClockSampler(local_rank) as cs_sus:
+        sus_ms = m.run_resident(sus_steps)
+    sus_ms = max_over_ranks(sus_ms)
+    sus_profs = [m.profile_resident() for _ in range(3)] if rank == 0 else []
 
     # ---- end to end through the public batch call: host codes in, host (pinned) waveforms out, every step.
     # Like the reference server's slots (tts-mio-server.cpp:2659-2670, one context clone per slot), `--e2e-slots`
@@ -227,27 +306,60 @@ def run_b200(args, rank, world, local_rank):
         tp = os.path.join(ROOT, "profiles", "gemm_traffic.json")
         if os.path.exists(tp):
             traffic = json.load(open(tp)).get("dram_bytes_per_launch")
-        line["roofline"] = {"bound": "tensor", "achieved": achieved, "peak": peaks["bf16_tflops_sustained"],
-                            "unit": "TFLOP/s", "frac": achieved / peaks["bf16_tflops_sustained"], "traffic": traffic,
-                            "peak_source": peaks["source"] + " (bf16 sustained: kernel timed inside a long step)",
+        tmeta = json.load(open(tp)) if os.path.exists(tp) else {}
+        sg_ms = float(np.median([q["gemm_ms"] for q in sus_profs]))
+        sus_achieved = p["gemm_flops"] / (sg_ms * 1e-3) / 1e12
+        line["sustained"] = {"value": sum_audio_all / (sus_ms * 1e-3), "unit": "audio-seconds/s", "steps": sus_steps,
+                             "ms_per_step": sus_ms, "seconds": sus_ms * sus_steps * 1e-3, "clocks": cs_sus.summary(),
+                             "gemm_tflops": sus_achieved, "gemm_frac_of_sustained_peak": sus_achieved / peaks["bf16_tflops_sustained"],
+                             "note": "same resident step repeated for >= 2.5 s: the numerator that belongs beside the "
+                                     "sustained bf16 peak (both under the power cap for seconds)"}
+        line["roofline"] = {"bound": "tensor", "achieved": achieved, "peak": peaks["bf16_tflops"],
+                            "unit": "TFLOP/s", "frac": achieved / peaks["bf16_tflops"], "traffic": traffic,
+                            "traffic_source": {k: tmeta.get(k) for k in ("captured", "code", "file") if k in tmeta} or None,
+                            "frac_of_sustained_peak": achieved / peaks["bf16_tflops_sustained"],
+                            "peak_sustained": peaks["bf16_tflops_sustained"],
+                            "peak_source": peaks["source"] + " (bf16 burst: the K-step timed region lasts a fraction of a "
+                                           "second; see `sustained` for the multi-second leg against the sustained peak)",
                             "kernel": "gemm_tcgen05_kernel", "launches_per_step": p["gemm_launches"],
                             "avg_launch_ms": g_ms / max(1, p["gemm_launches"]),
                             "flops_per_launch_avg": p["gemm_flops"] / max(1, p["gemm_launches"]),
                             "algorithmic_bytes_per_launch_avg": p["gemm_bytes"] / max(1, p["gemm_launches"]),
                             "gemm_share_of_step": g_ms / p["total_ms"],
                             "whole_path_frac": (U.FLOP_PER_TOKEN * BATCH * N_CODES / (ms * 1e-3) / 1e12)
-                            / peaks["bf16_tflops_sustained"] if world == 1 else None}
+                            / peaks["bf16_tflops"] if world == 1 else None}
         line["stages_ms"] = {k: p[k] for k in ("prenet_ms", "upsample_prior_ms", "decoder_ms", "post_head_ms", "istft_ms",
                                                "total_ms", "attn_ms")}
         if world == 1 and not args.skip_aux:
             line["aux"] = aux_configs(m, peaks)
         if world == 1 and not args.skip_cpu:
             # ---- CPU baseline: the unmodified reference on this box's host cores, bounded sample ----
-            n_cpu = BATCH   # the whole config-2 batch, one utterance after another (~10-30 s of host work)
-            v, cores, kind, dt = time_cpu_reference(n_cpu, N_CODES, warmup=1)
+            n_cpu = 24      # utterances 0..23 of the config-2 batch, one after another (~10 s of host work)
+            keep = (0, 17)
+            v, cores, kind, dt, ref_audio = time_cpu_reference(n_cpu, N_CODES, warmup=1, keep=keep)
             line["cpu_baseline"] = {"value": v, "unit": "audio-seconds/s", "cores": cores, "kind": kind,
-                                    "sample": f"{n_cpu} of the 64 utterances x {N_CODES} codes, sequential "
+                                    "sample": f"utterances 0..{n_cpu - 1} of the 64 x {N_CODES} codes, sequential "
                                               f"mio_tts_synthesize calls, {cores} threads, {dt:.1f} s"}
+            arr = cpu_arrangements() if kind == "reference" else None
+            if arr:
+                line["cpu_baseline"]["arrangements"] = arr
+                best = max(arr, key=lambda k: arr[k]["median"])
+                if arr[best]["median"] > v:     # report the arrangement that is kindest to the reference
+                    line["cpu_baseline"].update(value=arr[best]["median"], cores=cores, sample=(
+                        f"{best}: median of {arr[best]['runs']} runs, see arrangements (whole utterances of {N_CODES} codes)"))
+            # ---- parity of THIS run: the timed batch's waveforms against the reference's for the same codes ----
+            got, _ = m.synthesize_batch(codes, embs)
+            par = {}
+            for u in keep:
+                r, g = ref_audio[u].astype(np.float64), np.asarray(got[u], np.float64)
+                err = g - r
+                par[f"utt{u}"] = {"snr_db": float(10 * np.log10((r * r).sum() / max((err * err).sum(), 1e-300))),
+                                  "max_abs": float(np.abs(err).max()), "ref_peak": float(np.abs(r).max())}
+            line["parity_snr_db"] = min(x["snr_db"] for x in par.values())
+            line["parity_max_abs"] = max(x["max_abs"] for x in par.values())
+            line["parity"] = {"against": "oracle/_ref (unmodified reference, fp32 CPU) on the same codes + embedding"
+                              if kind == "reference" else "numpy oracle", "utterances": par,
+                              "linear_dtype": os.environ.get("MIO_TTS_B200_LINEAR_DTYPE", "bf16")}
         if json_fd is None:
             print(json.dumps(line), flush=True)
         else:
@@ -306,6 +418,8 @@ def main():
     ap.add_argument("--skip-cpu", action="store_true", help="omit the cpu_baseline leg (profiling runs)")
     ap.add_argument("--skip-aux", action="store_true", help="omit the config-3 / config-4 side measurements")
     ap.add_argument("--e2e-slots", type=int, default=2, help="host threads (context clones) of the end-to-end leg")
+    if len(sys.argv) > 1 and sys.argv[1] == "--cpu-worker":
+        return cpu_worker_main(sys.argv[2:])
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -58,8 +58,14 @@ struct mio_tts_params {    /* lib.h:20-25 (by value) */
 MIO_B200_API struct mio_tts_params mio_tts_default_params(void);
 
 /* lib.h:29-33, lib.cpp:814-848.  Loads the MioCodec GGUF (unchanged weight layout) and uploads re-tiled
- * weights to the device chosen by MIO_TTS_BACKEND_DEVICE ("CUDA<n>", default CUDA0).  `wavlm_model` is
- * accepted and remembered but not loaded (reference-audio embedding extraction is not part of this path). */
+ * weights to the device chosen by MIO_TTS_BACKEND_DEVICE ("CUDA<n>", default CUDA0).  With a non-empty
+ * `wavlm_model` the WavLM GGUF and the global-encoder tensors of the MioCodec GGUF are loaded to the same device
+ * and mio_tts_reference_to_embedding runs on the GPU; NULL / "" leaves that entry point failing with the
+ * reference's "WavLM model is not loaded".
+ * Ownership: waveforms (and WAV bodies of the mio_tts_b200_*wav16* calls) are PINNED host buffers taken from a
+ * process-wide result pool: hand them back with mio_tts_audio_free / mio_tts_b200_wav_free, never free().  The pool
+ * keeps returned slabs for reuse and is not shrunk (its high-water mark is the largest set of results alive at once).
+ * MIO_TTS_B200_MALLOC_OUTPUT=1 makes every result a plain malloc() buffer instead (pageable copy, slower). */
 MIO_B200_API struct mio_tts_context * mio_tts_init_from_file(const char * model_vocoder, const char * wavlm_model,
                                                              char * err, size_t err_size);
 
@@ -101,8 +107,10 @@ MIO_B200_API bool mio_tts_codes_save(const char * path, const int32_t * codes, s
                                      size_t err_size);
 MIO_B200_API void mio_tts_codes_free(int32_t * codes);
 
-/* lib.h:92-99, lib.cpp:1046-1125.  Not on the decode path (WavLM + global encoder):
- * fails with the reference's "WavLM model is not loaded" class of errors. */
+/* lib.h:92-99, lib.cpp:1046-1125.  WAV file -> speaker embedding on the GPU (WavLM SSL extractor + global encoder,
+ * SURVEY.md 8f N1/N2) when the context was created with a WavLM GGUF; otherwise the reference's "WavLM model is not
+ * loaded" error.  WAV (PCM16/24/32, float32) only: mp3/flac go through mio_tts_b200_reference_pcm_to_embedding_batch
+ * as decoded PCM.  *embedding_out is malloc'd: release with mio_tts_embedding_free. */
 MIO_B200_API bool mio_tts_reference_to_embedding(struct mio_tts_context * ctx, const char * reference_audio,
                                                  struct mio_tts_params params, float ** embedding_out,
                                                  size_t * n_embedding_out, char * err, size_t err_size);

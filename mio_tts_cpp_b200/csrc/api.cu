@@ -169,38 +169,51 @@ bool read_wav_mono(const std::string & path, std::vector<float> & out, int & sam
     return true;
 }
 
-// ---- text codes (lib.cpp:71-113, 225-286) ----
-std::string strip_ascii_punct(std::string s) {
-    while (!s.empty() && std::ispunct((unsigned char) s.front()) && s.front() != '<' && s.front() != '-') s.erase(s.begin());
-    while (!s.empty() && std::ispunct((unsigned char) s.back()) && s.back() != '>' && !std::isdigit((unsigned char) s.back())) s.pop_back();
-    return s;
+// ---- text codes ----
+// Spec (behaviour, not code): /root/reference/src/mio-tts-lib.cpp:79-113 (a code written as text: optional ASCII
+// punctuation around it, optional <|s_N|> wrapper, then what std::stoll accepts in full, within int32) and :115-138
+// (a vocabulary piece: exactly <|s_N|>, N what strtol accepts up to the first NUL, 0 <= N <= INT32_MAX).
+// One pointer scanner serves both: [space]* [+-]? digit+ to the end of the range, no int64 overflow.
+bool scan_decimal(const char * p, const char * end, long long & value) {
+    while (p < end && (*p == ' ' || (*p >= '\t' && *p <= '\r'))) ++p;
+    bool neg = false;
+    if (p < end && (*p == '+' || *p == '-')) neg = *p++ == '-';
+    if (p == end) return false;
+    const unsigned long long lim = neg ? 9223372036854775808ull : 9223372036854775807ull;
+    unsigned long long mag = 0;
+    for (; p < end; ++p) {
+        const unsigned d = (unsigned) (unsigned char) *p - (unsigned) '0';
+        if (d > 9 || mag > (lim - d) / 10) return false;
+        mag = mag * 10 + d;
+    }
+    value = neg ? (long long) (0ull - mag) : (long long) mag;
+    return true;
 }
 
 bool parse_code_token(const std::string & raw, int32_t & out) {
-    std::string token = strip_ascii_punct(raw);
-    if (token.empty()) return false;
-    if (token.rfind("<|s_", 0) == 0 && token.size() > 6 && token.substr(token.size() - 2) == "|>") token = token.substr(4, token.size() - 6);
-    try {
-        size_t used = 0;
-        const long long v = std::stoll(token, &used, 10);
-        if (used != token.size()) return false;
-        if (v < (long long) std::numeric_limits<int32_t>::min() || v > (long long) std::numeric_limits<int32_t>::max()) return false;
-        out = (int32_t) v;
-        return true;
-    } catch (...) {
-        return false;
-    }
+    auto punct = [](unsigned char c) {      // "C" locale ispunct
+        return (c >= 33 && c <= 47) || (c >= 58 && c <= 64) || (c >= 91 && c <= 96) || (c >= 123 && c <= 126);
+    };
+    const char * b = raw.data(), * e = b + raw.size();
+    while (b < e && punct((unsigned char) *b) && *b != '<' && *b != '-') ++b;
+    while (e > b && punct((unsigned char) e[-1]) && e[-1] != '>') --e;
+    if (b == e) return false;
+    if (e - b > 6 && std::memcmp(b, "<|s_", 4) == 0 && e[-2] == '|' && e[-1] == '>') { b += 4; e -= 2; }
+    long long v = 0;
+    if (!scan_decimal(b, e, v) || v < INT32_MIN || v > INT32_MAX) return false;
+    out = (int32_t) v;
+    return true;
 }
 
-bool parse_codec_piece(const std::string & piece, int32_t & code) {   // lib.cpp:115-138
-    if (piece.size() < 6 || piece.compare(0, 4, "<|s_") != 0) return false;
-    if (piece[piece.size() - 2] != '|' || piece.back() != '>') return false;
-    const std::string num = piece.substr(4, piece.size() - 6);
-    if (num.empty()) return false;
-    char * end = nullptr;
-    const long value = std::strtol(num.c_str(), &end, 10);
-    if (end == nullptr || *end != '\0' || value < 0 || value > std::numeric_limits<int32_t>::max()) return false;
-    code = (int32_t) value;
+bool parse_codec_piece(const std::string & piece, int32_t & code) {
+    const size_t n = piece.size();
+    if (n < 7 || std::memcmp(piece.data(), "<|s_", 4) != 0 || piece[n - 2] != '|' || piece[n - 1] != '>') return false;
+    const char * b = piece.data() + 4;
+    const char * e = (const char *) std::memchr(b, 0, n - 6);
+    if (e == nullptr) e = piece.data() + n - 2;
+    long long v = 0;
+    if (!scan_decimal(b, e, v) || v < 0 || v > INT32_MAX) return false;
+    code = (int32_t) v;
     return true;
 }
 
@@ -337,20 +350,33 @@ bool mio_tts_context_set_backend_device(struct mio_tts_context * ctx, const char
     }
     if (dev == -1 || dev == ctx->mdl->device) return true;
     return guarded(err, err_size, [&] {
-        std::lock_guard<std::mutex> lk(ctx->eng->mtx);
+        // The objects being replaced own the mutex that guards them, so they are parked in locals declared BEFORE the
+        // guard: they are destroyed after it has unlocked (and only once the new ones are in place).
+        std::unique_ptr<engine> old_eng, old_eng2;
+        std::unique_ptr<refenc> old_renc;
+        std::shared_ptr<batcher> old_bat;
         std::string load_err;
         auto m = load_model(ctx->vocoder_path, dev, load_err);
         if (!m) throw std::runtime_error("decoder backend setup failed: " + load_err);
         auto r = load_refmodel(ctx->vocoder_path, ctx->wavlm_path, dev, m->hp.decoder_adanorm_dim, load_err);
         if (!r) throw std::runtime_error("wavlm backend setup failed: " + load_err);
-        ctx->eng.reset();
-        ctx->eng2.reset();
-        ctx->renc.reset();
-        ctx->mdl = m;
-        ctx->ref = r;
-        ctx->eng.reset(new engine(m));
-        ctx->renc.reset(new refenc(r));
-        if (ctx->bat) ctx->bat = std::make_shared<batcher>(m, ctx->bat->max_batch, ctx->bat->max_wait_us, ctx->bat->workers);
+        std::unique_ptr<engine> new_eng(new engine(m));
+        std::unique_ptr<refenc> new_renc(new refenc(r));
+        std::shared_ptr<batcher> new_bat;
+        if (ctx->bat) new_bat = std::make_shared<batcher>(m, ctx->bat->max_batch, ctx->bat->max_wait_us, ctx->bat->workers);
+        {
+            std::lock_guard<std::mutex> lk(ctx->eng->mtx);
+            std::lock_guard<std::mutex> lk2(ctx->eng2_mtx);
+            old_eng = std::move(ctx->eng);
+            old_eng2 = std::move(ctx->eng2);
+            old_renc = std::move(ctx->renc);
+            old_bat = std::move(ctx->bat);
+            ctx->mdl = m;
+            ctx->ref = r;
+            ctx->eng = std::move(new_eng);
+            ctx->renc = std::move(new_renc);
+            ctx->bat = new_bat;
+        }
     });
 }
 

@@ -105,7 +105,7 @@ bool gguf_file::load(const std::string & path, std::string & err) {
                 for (uint64_t j = 0; j < n && c.ok; ++j) c.str();
             } else {
                 const size_t es = scalar_size(et);
-                if (es == 0 || (uint64_t) (c.end - c.p) < n * es) { c.ok = false; break; }
+                if (es == 0 || n > (uint64_t) (c.end - c.p) / es) { c.ok = false; break; }
                 c.p += n * es;
             }
         } else if (!read_scalar(c, kv.type, kv)) {
@@ -134,8 +134,12 @@ bool gguf_file::load(const std::string & path, std::string & err) {
         gguf_tensor & t = tensors_[i];
         const size_t es = type_size(t.type);
         if (es == 0) { err = "unsupported tensor type in GGUF: " + t.name; return false; }
-        const uint64_t bytes = (uint64_t) t.nelements() * es;
-        if (data_start + t.offset + bytes > blob_.size()) { err = "failed to load GGUF"; return false; }
+        uint64_t bytes = 0;
+        if (!t.checked_bytes(es, bytes) || data_start > blob_.size() || t.offset > blob_.size() - data_start ||
+            bytes > blob_.size() - data_start - t.offset) {
+            err = "failed to load GGUF";
+            return false;
+        }
         t.data = blob_.data() + data_start + t.offset;
         index_[t.name] = i;
     }

@@ -21,6 +21,17 @@ struct gguf_tensor {
     uint64_t offset = 0;       // relative to the data section
     const uint8_t * data = nullptr;
     int64_t nelements() const { int64_t n = 1; for (auto d : ne) n *= d; return n; }
+    // element count with every dimension > 0 and no 64-bit overflow of count * elem_size; false otherwise
+    bool checked_bytes(size_t elem_size, uint64_t & bytes) const {
+        uint64_t n = 1;
+        for (auto d : ne) {
+            if (d <= 0 || (uint64_t) d > UINT64_MAX / n) return false;
+            n *= (uint64_t) d;
+        }
+        if (elem_size == 0 || n > UINT64_MAX / elem_size) return false;
+        bytes = n * elem_size;
+        return true;
+    }
 };
 
 struct gguf_kv {

@@ -100,12 +100,13 @@ class RefLib:
 
     def decode_spec(self, h, codes, emb, n_threads=1, flash=-1):
         codes = np.ascontiguousarray(codes, dtype=np.int32)
-        emb = np.ascontiguousarray(emb, dtype=np.float32)
+        emb = np.ascontiguousarray(emb if emb is not None else [], dtype=np.float32)   # None: static model
         out = C.POINTER(C.c_float)()
         nf, nb = C.c_int(0), C.c_int(0)
         err = C.create_string_buffer(512)
         ok = self.lib.ref_decoder_decode(h, codes.ctypes.data_as(C.POINTER(C.c_int32)), codes.size,
-                                         emb.ctypes.data_as(C.POINTER(C.c_float)), emb.size, n_threads, flash,
+                                         emb.ctypes.data_as(C.POINTER(C.c_float)) if emb.size else None, emb.size,
+                                         n_threads, flash,
                                          C.byref(out), C.byref(nf), C.byref(nb), err, 512)
         if not ok:
             raise RuntimeError("ref decode_tokens: " + err.value.decode())
@@ -192,13 +193,13 @@ class RefLib:
 
     def synthesize(self, ctx, codes, emb, n_threads=0, flash=-1):
         codes = np.ascontiguousarray(codes, dtype=np.int32)
-        emb = np.ascontiguousarray(emb, dtype=np.float32)
+        emb = np.ascontiguousarray(emb if emb is not None else [], dtype=np.float32)   # None: static model
         prm = MioTtsParams(n_threads, 20.0, -1, flash)
         out = C.POINTER(C.c_float)()
         n, sr = C.c_size_t(0), C.c_int32(0)
         err = C.create_string_buffer(512)
         ok = self.lib.mio_tts_synthesize(ctx, codes.ctypes.data_as(C.POINTER(C.c_int32)), codes.size,
-                                         emb.ctypes.data_as(C.POINTER(C.c_float)), emb.size, prm,
+                                         emb.ctypes.data_as(C.POINTER(C.c_float)) if emb.size else None, emb.size, prm,
                                          C.byref(out), C.byref(n), C.byref(sr), err, 512)
         if not ok:
             raise RuntimeError("mio_tts_synthesize: " + err.value.decode())

@@ -52,5 +52,19 @@ def load_golden(name):
     return np.load(os.path.join(GOLD, name + ".npz"))
 
 
-GOLDEN_CASES = ["tiny_T50", "tiny_T1", "tiny_T133", "upsampler_tiny_T20", "default_T24", "upsampler_T12"]
+GOLDEN_CASES = ["tiny_T50", "tiny_T1", "tiny_T133", "upsampler_tiny_T20", "default_T24", "upsampler_T12",
+                "tiny_lerp3_T37", "tiny_lerp15_T41", "tiny_static_T50"]
+# BASELINE configs 1 / 2 at full size: utterances 0 / 17 / 63 of the bench batch, reduced (tools/gen_golden.py FULL_CASES)
+FULL_CASES = ["default_T400", "default_T400_u17", "default_T400_u63"]
+
+
+def case_embedding(z, emb):
+    """Static (dynamic_global = 0) fixtures take no embedding (lib.cpp:1222-1225)."""
+    return None if "static" in str(z["preset"]) else emb
+
+
+def full_case_audio_windows(z, audio):
+    """The samples of `audio` that a reduced full-size fixture kept (concatenated windows)."""
+    w = int(z["audio_window"])
+    return np.concatenate([audio[int(s):int(s) + w] for s in z["audio_starts"]])
 ISTFT_CASES = ["istft_120_30", "istft_392_98", "istft_1280_320", "istft_1920_480", "istft_2048_512"]

@@ -54,6 +54,59 @@ def test_codes_roundtrip_and_token_forms(tmp_path):
     assert L.codes_load(p).tolist() == [5, 7, 12, 42]
 
 
+# token -> parsed value (None: "failed to parse code token").  The accepted language is the reference's
+# (lib.cpp:79-113): ASCII punctuation stripped on both sides except a leading '<' / '-' and a trailing '>', optional
+# <|s_N|> wrapper, then exactly what std::stoll takes in full, within int32.
+TOKEN_FORMS = [("17", 17), ("+17", 17), ("0017", 17), ("<|s_17|>", 17), ("(17)", 17), ('"17",', 17), ("[<|s_9|>]", 9),
+               ("<|s_+4|>", 4), ("<|s_|>", None), ("<|s_1x|>", None), ("1x", None), ("x1", None), ("--1", None),
+               ("<17>", None), ("1.5", None), ("99999999999", None), ("9223372036854775808", None), ("+", None),
+               ("!!!", None), ("<|s_12799|>;", 12799), ("#12", 12), ("12#", 12), ("12_", 12), ("_12", 12)]
+
+
+def _load_one(tmp_path, loader, tok):
+    p = str(tmp_path / "t.txt")
+    open(p, "w").write(tok + "\n")
+    try:
+        return [int(x) for x in loader(p)]
+    except Exception as e:
+        return str(e).split(": ")[0] if "failed to parse" in str(e) else str(e)
+
+
+def test_code_token_language(tmp_path):
+    for tok, want in TOKEN_FORMS:
+        got = _load_one(tmp_path, L.codes_load, tok)
+        if tok == "!!!":
+            assert got == "codes input file is empty" or got == "failed to parse code token", (tok, got)
+        else:
+            assert got == ([want] if want is not None else "failed to parse code token"), (tok, got)
+
+
+def test_code_token_language_matches_live_reference(tmp_path):
+    """Same strings through the compiled reference's own mio_tts_codes_load when oracle/_ref is in this checkout."""
+    import ctypes as C
+
+    from oracle.refbind import RefLib, ref_lib_path
+
+    if ref_lib_path() is None:
+        pytest.skip("oracle/_ref not built in this checkout")
+    R = RefLib().lib
+    R.mio_tts_codes_load.restype = C.c_bool
+    R.mio_tts_codes_load.argtypes = [C.c_char_p, C.POINTER(C.POINTER(C.c_int32)), C.POINTER(C.c_size_t), C.c_char_p, C.c_size_t]
+    R.mio_tts_codes_free.argtypes = [C.POINTER(C.c_int32)]
+
+    def ref_load(path):
+        out, n, err = C.POINTER(C.c_int32)(), C.c_size_t(0), C.create_string_buffer(256)
+        if not R.mio_tts_codes_load(path.encode(), C.byref(out), C.byref(n), err, 256):
+            raise RuntimeError(err.value.decode())
+        v = [out[i] for i in range(n.value)]
+        R.mio_tts_codes_free(out)
+        return v
+
+    extra = ["-0", "<|s_-0|>", "0x10", "1e3", "<|s_5|", "|s_5|>", "<|s_ 5|>", "12-", "-12-", "'<|s_3|>'", "<<|s_3|>>"]
+    for tok in [t for t, _ in TOKEN_FORMS] + extra:
+        assert _load_one(tmp_path, L.codes_load, tok) == _load_one(tmp_path, ref_load, tok), tok
+
+
 @pytest.mark.parametrize("text,msg", [("", "codes input file is empty"), ("12800\n", "code id out of range in input file"),
                                       ("-1\n", "code id out of range in input file"),
                                       ("abc\n", "failed to parse code token: abc")])

@@ -9,7 +9,7 @@ import os
 import numpy as np
 import pytest
 
-from conftest import GOLDEN_CASES, ISTFT_CASES, load_golden, snr_db
+from conftest import FULL_CASES, GOLDEN_CASES, ISTFT_CASES, case_embedding, full_case_audio_windows, load_golden, snr_db
 from oracle import miocodec_np as O
 
 
@@ -19,6 +19,7 @@ def test_decode_matches_reference_fixture(name, gguf_paths, emb):
     path, sha = gguf_paths(str(z["preset"]))
     assert sha == str(z["weights_sha256"]), "synthetic weight generator drifted from the fixture"
     m = O.Model(path)
+    emb = case_embedding(z, emb)
     spec = O.decode_tokens(m, z["codes"], emb)
     assert spec.shape == z["spec"].shape
     # fp32 re-association (numpy BLAS vs ggml) plus fp16 rounding-boundary flips in the conv operands: measured
@@ -29,6 +30,22 @@ def test_decode_matches_reference_fixture(name, gguf_paths, emb):
     assert audio.shape == z["audio"].shape
     assert int(z["sample_rate"]) == m.hp["sample_rate"]
     assert snr_db(audio, z["audio"]) > 50.0
+
+
+@pytest.mark.parametrize("name", FULL_CASES)
+def test_full_size_decode_matches_reference_fixture(name, gguf_paths, emb):
+    """Default hyper-parameters, 400 codes (BASELINE configs 1 / 2): window-65 band mask with real masking over 800
+    frames, RoPE positions to 799, GroupNorm over 800 x 512."""
+    z = load_golden(name)
+    path, sha = gguf_paths("default")
+    assert sha == str(z["weights_sha256"])
+    m = O.Model(path)
+    spec = O.decode_tokens(m, z["codes"], emb)
+    assert spec.shape[0] == int(z["n_frames"])
+    assert snr_db(spec[::int(z["spec_stride"])], z["spec"]) > 60.0
+    audio = O.peak_normalize(O.istft(spec, m.hp["n_fft"], m.hp["hop_length"]))
+    assert audio.size == int(z["n_audio"])
+    assert snr_db(full_case_audio_windows(z, audio), z["audio"]) > 50.0
 
 
 @pytest.mark.parametrize("name", ISTFT_CASES)

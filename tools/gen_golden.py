@@ -35,7 +35,19 @@ CASES = [  # (fixture, preset, T, codes seed)
     ("upsampler_tiny_T20", "upsampler_tiny", 20, 42),
     ("default_T24", "default", 24, 42),
     ("upsampler_T12", "upsampler", 12, 42),
+    # frames != 2T: the lerp branch of ggml_interpolate (three frames per token; 1.5 with an odd T)
+    ("tiny_lerp3_T37", "tiny_lerp3", 37, 42),
+    ("tiny_lerp15_T41", "tiny_lerp15", 41, 42),
+    # dynamic_global = 0: plain-LayerNorm decoder, no embedding accepted
+    ("tiny_static_T50", "tiny_static", 50, 42),
 ]
+STATIC_PRESETS = {"tiny_static"}
+
+# BASELINE configs 1 / 2 at full size (default hyper-parameters, 400 codes, en_female): utterances 0 / 17 / 63 of the
+# bench batch (codes seed 42 + i).  Reduced: every SPEC_STRIDE-th spectrogram frame; the whole waveform for utterance 0,
+# three 1-second windows for the others.
+FULL_CASES = [("default_T400", 42, None), ("default_T400_u17", 59, 24000), ("default_T400_u63", 105, 24000)]
+SPEC_STRIDE = 8
 
 
 def main():
@@ -53,15 +65,37 @@ def main():
             cache[preset] = (path, write_gguf(path, preset, 0)[0])
         path, sha = cache[preset]
         codes = np.random.default_rng(seed).integers(0, 12800, T).astype(np.int32)
+        e = None if preset in STATIC_PRESETS else emb
         h = R.open_decoder(path)
-        spec = R.decode_spec(h, codes, emb, n_threads=1, flash=0)
+        spec = R.decode_spec(h, codes, e, n_threads=1, flash=0)
         R.close_decoder(h)
         ctx = R.open_context(path)
-        audio, sr = R.synthesize(ctx, codes, emb, n_threads=1, flash=0)
+        audio, sr = R.synthesize(ctx, codes, e, n_threads=1, flash=0)
         R.close_context(ctx)
         np.savez_compressed(os.path.join(out_dir, name + ".npz"), preset=preset, weights_sha256=sha, codes=codes,
                             spec=spec, audio=audio, sample_rate=sr)
         print(name, spec.shape, audio.shape, sr, float(np.abs(audio).max()))
+    if "default" not in cache:
+        cache["default"] = ("/tmp/mio_golden_default.gguf", write_gguf("/tmp/mio_golden_default.gguf", "default", 0)[0])
+    path, sha = cache["default"]
+    ctx = R.open_context(path)
+    h = R.open_decoder(path)
+    for name, seed, win in FULL_CASES:
+        codes = np.random.default_rng(seed).integers(0, 12800, 400).astype(np.int32)
+        spec = R.decode_spec(h, codes, emb, n_threads=8, flash=0)
+        audio, sr = R.synthesize(ctx, codes, emb, n_threads=8, flash=0)
+        if win is None:
+            starts, kept = np.array([0]), audio
+        else:
+            starts = np.array([0, (audio.size // 2 // win) * win, audio.size - win])
+            kept = np.concatenate([audio[s:s + win] for s in starts])
+        np.savez_compressed(os.path.join(out_dir, name + ".npz"), preset="default", weights_sha256=sha, codes=codes,
+                            spec_stride=SPEC_STRIDE, n_frames=spec.shape[0], spec=spec[::SPEC_STRIDE],
+                            audio_starts=starts, audio_window=win if win else audio.size, audio=kept,
+                            n_audio=audio.size, sample_rate=sr, audio_peak=float(np.abs(audio).max()))
+        print(name, spec.shape, audio.shape, sr, float(np.abs(audio).max()))
+    R.close_decoder(h)
+    R.close_context(ctx)
     # iSTFT-only fixture: the reference's embd_to_audio on BASELINE config-3 style spectra
     rng = np.random.default_rng(7)
     for n_fft, hop, frames in ((1920, 480, 12), (392, 98, 30), (120, 30, 5), (2048, 512, 3), (1280, 320, 4)):

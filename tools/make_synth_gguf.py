@@ -41,6 +41,25 @@ PRESETS = {
                            decoder_layers=1, decoder_dim=128, decoder_heads=2, decoder_ff=256, decoder_window=9,
                            decoder_adanorm_dim=128, resnet_blocks=1, resnet_groups=32,
                            up_factors=[3, 3], up_kernels=[7, 5], up_channels=[64, 32], up_out=48),
+    # frames != 2*T: the lerp branch of ggml_interpolate (/root/reference/src/miocodec-decoder.cpp:1097-1103,1373),
+    # three frames per token (upward) and 1.5 frames per token (downward, odd T leaves a remainder)
+    "tiny_lerp3": dict(sample_rate=24000, n_fft=120, hop_length=30, samples_per_token=90,
+                       prenet_layers=1, prenet_dim=128, prenet_heads=2, prenet_ff=256, prenet_window=9,
+                       decoder_layers=1, decoder_dim=128, decoder_heads=2, decoder_ff=256, decoder_window=9,
+                       decoder_adanorm_dim=128, resnet_blocks=1, resnet_groups=32,
+                       up_factors=[], up_kernels=[], up_channels=[]),
+    "tiny_lerp15": dict(sample_rate=24000, n_fft=120, hop_length=30, samples_per_token=45,
+                        prenet_layers=1, prenet_dim=128, prenet_heads=2, prenet_ff=256, prenet_window=9,
+                        decoder_layers=1, decoder_dim=128, decoder_heads=2, decoder_ff=256, decoder_window=9,
+                        decoder_adanorm_dim=128, resnet_blocks=1, resnet_groups=32,
+                        up_factors=[], up_kernels=[], up_channels=[]),
+    # dynamic_global = 0: plain LayerNorm weights in the decoder blocks and tail instead of the AdaLN condition
+    # linears (/root/reference/src/miocodec-decoder.cpp:662-674, 701-711, 1190-1291, 1390-1400)
+    "tiny_static": dict(sample_rate=24000, n_fft=120, hop_length=30, samples_per_token=60, dynamic_global=0,
+                        prenet_layers=2, prenet_dim=128, prenet_heads=2, prenet_ff=256, prenet_window=9,
+                        decoder_layers=2, decoder_dim=128, decoder_heads=2, decoder_ff=256, decoder_window=9,
+                        decoder_adanorm_dim=128, resnet_blocks=1, resnet_groups=32,
+                        up_factors=[], up_kernels=[], up_channels=[]),
 }
 VOCAB = 12800  # codes 0..12799, /root/reference/src/mio-tts-lib.cpp:30-31
 
@@ -115,18 +134,27 @@ def synth_tensors(cfg, seed=0):
         yield from resblk(f"wave_post.{j}", dd)
     for i in range(cfg["decoder_layers"]):
         p = f"wave_decoder.blk.{i}."
-        for n in ("attn_cond", "ffn_cond"):
-            yield p + n + ".weight", lin(3 * dd, ad, 0.5)
-            b = small(3 * dd)
-            b[2 * dd:] += 0.5  # gate ~ 0.5 so every block contributes
-            yield p + n + ".bias", b
+        if cfg.get("dynamic_global", 1):
+            for n in ("attn_cond", "ffn_cond"):
+                yield p + n + ".weight", lin(3 * dd, ad, 0.5)
+                b = small(3 * dd)
+                b[2 * dd:] += 0.5  # gate ~ 0.5 so every block contributes
+                yield p + n + ".bias", b
+        else:
+            for n in ("attn_norm", "ffn_norm"):
+                yield p + n + ".weight", norm_w(dd)
+                yield p + n + ".bias", small(dd)
         for n in ("attn_q", "attn_k", "attn_v", "attn_output"):
             yield p + n + ".weight", lin(dd, dd)
         yield p + "ffn_gate.weight", lin(df, dd)
         yield p + "ffn_up.weight", lin(df, dd)
         yield p + "ffn_down.weight", lin(dd, df)
-    yield "wave_decoder.norm_cond.weight", lin(2 * dd, ad, 0.5)
-    yield "wave_decoder.norm_cond.bias", small(2 * dd)
+    if cfg.get("dynamic_global", 1):
+        yield "wave_decoder.norm_cond.weight", lin(2 * dd, ad, 0.5)
+        yield "wave_decoder.norm_cond.bias", small(2 * dd)
+    else:
+        yield "wave_decoder.norm.weight", norm_w(dd)
+        yield "wave_decoder.norm.bias", small(dd)
     c_in = dd
     for i, (f, k, c_out) in enumerate(zip(cfg["up_factors"], cfg["up_kernels"], cfg["up_channels"])):
         yield f"wave_upsampler.up.{i}.weight", (rng.standard_normal((c_in, c_out, k)) / np.sqrt(c_in * k / f)).astype(f32)
@@ -278,7 +306,7 @@ def write_gguf(path, preset="default", seed=0, global_encoder=None):
     w.add_name(f"MioCodec decoder synthetic ({preset}, seed {seed})")
     u32 = w.add_uint32
     u32("miocodec.model_type", 0)
-    u32("miocodec.dynamic_global", 1)
+    u32("miocodec.dynamic_global", int(cfg.get("dynamic_global", 1)))
     for k in ("sample_rate", "n_fft", "hop_length", "samples_per_token",
               "prenet_layers", "prenet_dim", "prenet_heads", "prenet_ff", "prenet_window",
               "decoder_layers", "decoder_dim", "decoder_heads", "decoder_ff", "decoder_window",
