@@ -100,7 +100,16 @@ struct gemm_args {
     const int * row_pos;                 // row -> position in utterance (needed with rope)
     const float2 * rope;                 // [pos, head_dim/2] (cos, sin)
     int rope_cols, head_dim;             // columns [0, rope_cols) = q,k: rotated in (even, odd) pairs per head
+    // EPI_STORE32 only: the GroupNorm that consumes this output gets its per-(utterance, group) sum / sum of squares
+    // from the epilogue (double atomics on gn_stats[(utt * gn_groups + g) * 2 + {0,1}], gap rows excluded) instead of
+    // a separate pass over the output.  Needs row_utt, N % 32 == 0 and N / gn_groups == 16 or a multiple of 32.
+    double * gn_stats; int gn_groups;
 };
+inline bool gemm_gn_stats_ok(int N, int groups) {
+    if (groups <= 0 || N % groups != 0 || N % 32 != 0) return false;
+    const int cpg = N / groups;
+    return cpg == 16 || cpg % 32 == 0;
+}
 
 void gemm_launch(const gemm_args & a, int num_sms, cudaStream_t st);
 // A-operand / weight tensor maps (row-major [rows, cols] 16-bit, cols contiguous)
@@ -123,12 +132,10 @@ void launch_layernorm(const float * x, int rows, int dim, float eps, const float
 void launch_cast16(const float * x, void * out16, int out_dtype, size_t n, cudaStream_t st);
 void launch_gn_stats(const float * x, int dim, int groups, const row_tile * tiles, int n_tiles, double * stats,
                      cudaStream_t st);
-// (sum, sumsq) -> (mean, rstd) per (utterance, group)
-void launch_gn_finalize(const double * stats, const int * utt_len, int cpg, int groups, int n_utt, float eps,
-                        float2 * mean_rstd, cudaStream_t st);
-// normalise + affine + SiLU -> 16-bit conv operand; gap rows of the layout are written as zeros
-void launch_gn_apply(const float * x, int rows, int dim, int groups, const float2 * mean_rstd, const float * w,
-                     const float * b, const int * row_utt, void * out16, int out_dtype, cudaStream_t st);
+// (sum, sumsq) -> (mean, rstd) per (utterance, group), then normalise + affine + SiLU -> 16-bit conv operand; gap rows
+// of the layout are written as zeros
+void launch_gn_apply(const float * x, int rows, int dim, int groups, const double * stats, const int * utt_len, float eps,
+                     const float * w, const float * b, const int * row_utt, void * out16, int out_dtype, cudaStream_t st);
 // ggml_interpolate(bilinear, width only) from the x2 transposed-conv output to the decoder frame layout
 void launch_interp(const float * src, const int * src_row0, const int * src_len, float * dst, int rows, int dim,
                    const int * row_utt, const int * row_pos, const int * utt_len, cudaStream_t st);

@@ -95,7 +95,7 @@ engine::engine(std::shared_ptr<model> m) : mdl(std::move(m)) {
 engine::~engine() {
     cudaSetDevice(mdl->device);
     if (st_) cudaStreamSynchronize(st_);
-    for (dbuf * b : {&xt_, &fx_, &fy_, &ft_, &act16_, &qkv16_, &att16_, &ff16_, &cond_, &gn_stats_, &gn_mr_, &spec_buf_,
+    for (dbuf * b : {&xt_, &fx_, &fy_, &ft_, &act16_, &qkv16_, &att16_, &ff16_, &cond_, &gn_stats_, &spec_buf_,
                      &audio_, &peak_, &pcm_, &d_blob_})
         if (b->p) cudaFree(b->p);
     if (h_blob_) cudaFreeHost(h_blob_);
@@ -125,7 +125,7 @@ void engine::ensure(dbuf & b, size_t bytes) {
 
 size_t engine::workspace_bytes() const {
     size_t s = 0;
-    for (const dbuf * b : {&xt_, &fx_, &fy_, &ft_, &act16_, &qkv16_, &att16_, &ff16_, &cond_, &gn_stats_, &gn_mr_,
+    for (const dbuf * b : {&xt_, &fx_, &fy_, &ft_, &act16_, &qkv16_, &att16_, &ff16_, &cond_, &gn_stats_,
                            &spec_buf_, &audio_, &peak_, &pcm_, &d_blob_})
         s += b->cap;
     return s;
@@ -349,7 +349,6 @@ void engine::prepare(const int32_t * const * codes, const size_t * n_codes, cons
     ensure(ff16_, std::max(std::max(RT * hp.prenet_ff, RF * hp.decoder_ff), RT * dd) * 2);
     ensure(cond_, std::max<size_t>(16, batch * (size_t) mdl->cond_total * 4));
     ensure(gn_stats_, std::max<size_t>(16, (size_t) n_gn_slots_ * batch * gmax * 2 * sizeof(double)));
-    ensure(gn_mr_, batch * (size_t) gmax * sizeof(float2));
     ensure(spec_buf_, RS * spec_pitch_ * 4);
     ensure(audio_, (size_t) audio_total_ * 4 + 256);
     ensure(peak_, batch * 4);
@@ -396,7 +395,7 @@ void engine::reserve(int n_codes, int batch) {
 // -------------------------------------------------------------------------------------------------
 void engine::gemm(const dbuf & a, const dev_linear & w, int M, int epilogue, void * out, int ldo, int out_dtype,
                   const float * bias, const float * res, int ldr, const float * gate, const seq_layout * lay,
-                  const float2 * rope, int heads) {
+                  const float2 * rope, int heads, double * gn_stats, int gn_groups) {
     gemm_args g;
     std::memset(&g, 0, sizeof(g));
     g.map_a = amap(a, w.K);
@@ -409,6 +408,7 @@ void engine::gemm(const dbuf & a, const dev_linear & w, int M, int epilogue, voi
     g.gate = gate; g.gate_ld = mdl->cond_total;
     g.row_utt = lay ? lay->d_row_utt : nullptr;
     g.row_pos = lay ? lay->d_row_pos : nullptr;
+    g.gn_stats = gn_stats; g.gn_groups = gn_groups;
     if (epilogue == EPI_ROPE16) {
         const int dim = w.N / 3;
         g.rope = rope; g.rope_cols = 2 * dim; g.head_dim = dim / heads;   // (the 1/sqrt(head_dim) q scale lives in Wq)
@@ -463,23 +463,33 @@ void engine::run_tblock(float * x, const seq_layout & L, const tblock & blk, int
     gemm(ff16_, blk.down, rows, EPI_STORE32, x, dim, 0, nullptr, x, dim, cond ? cv + blk.cond_ffn_off + 2 * dim : nullptr, &L);
 }
 
+// GroupNorm + SiLU -> 16-bit conv operand.  The per-(utterance, group) sums of slot `slot` either were accumulated by the
+// epilogue of the GEMM that produced x (stats_ready) or come from one pass over x here.
 void engine::group_norm_silu(const float * x, const seq_layout & L, int channels, int groups, const dev_norm & n,
-                             int & gn_slot) {
-    double * stats = (double *) gn_stats_.p + (size_t) gn_slot * n_utt_ * gn_groups_max_ * 2;
-    ++gn_slot;
-    launch_gn_stats(x, channels, groups, L.d_tiles, L.n_tiles, stats, st_);
-    launch_gn_finalize(stats, L.d_len, channels / groups, groups, n_utt_, mdl->hp.group_norm_eps, (float2 *) gn_mr_.p, st_);
-    launch_gn_apply(x, L.rows, channels, groups, (const float2 *) gn_mr_.p, n.w, n.b, L.d_row_utt, act16_.p,
+                             int slot, bool stats_ready) {
+    double * stats = gn_slot_ptr(slot);
+    if (!stats_ready) launch_gn_stats(x, channels, groups, L.d_tiles, L.n_tiles, stats, st_);
+    launch_gn_apply(x, L.rows, channels, groups, stats, L.d_len, mdl->hp.group_norm_eps, n.w, n.b, L.d_row_utt, act16_.p,
                     mdl->conv_dtype, st_);
 }
 
-// resnet_block_eval, /root/reference/src/miocodec-decoder.cpp:1293-1330 (x updated in place, y is scratch)
-void engine::run_resblock(float *& x, float *& y, const seq_layout & L, const resblock & rb, int & gn_slot) {
+// resnet_block_eval, /root/reference/src/miocodec-decoder.cpp:1293-1330 (x updated in place, y is scratch).
+// in_ready: the producer of x already accumulated norm1's statistics into slot gn_slot; feeds_next: the next kernel is
+// another resnet block's norm1 on this block's output, so conv2's epilogue accumulates them (returned as in_ready).
+bool engine::run_resblock(float *& x, float *& y, const seq_layout & L, const resblock & rb, int & gn_slot, bool in_ready,
+                          bool feeds_next) {
+    static const bool fuse_env = [] { const char * e = std::getenv("MIO_TTS_B200_GN_FUSE"); return !(e && e[0] == '0'); }();
     const int c = rb.channels;
-    group_norm_silu(x, L, c, rb.groups, rb.n1, gn_slot);
-    gemm(act16_, rb.c1, L.rows, EPI_STORE32, y, c, 0, rb.c1.bias, nullptr, 0, nullptr, &L);
-    group_norm_silu(y, L, c, rb.groups, rb.n2, gn_slot);
-    gemm(act16_, rb.c2, L.rows, EPI_STORE32, x, c, 0, rb.c2.bias, x, c, nullptr, &L);
+    const bool fuse = fuse_env && gemm_gn_stats_ok(c, rb.groups);
+    const int s1 = gn_slot++, s2 = gn_slot++;
+    group_norm_silu(x, L, c, rb.groups, rb.n1, s1, in_ready);
+    gemm(act16_, rb.c1, L.rows, EPI_STORE32, y, c, 0, rb.c1.bias, nullptr, 0, nullptr, &L, nullptr, 0,
+         fuse ? gn_slot_ptr(s2) : nullptr, rb.groups);
+    group_norm_silu(y, L, c, rb.groups, rb.n2, s2, fuse);
+    const bool next_ready = fuse && feeds_next;
+    gemm(act16_, rb.c2, L.rows, EPI_STORE32, x, c, 0, rb.c2.bias, x, c, nullptr, &L, nullptr, 0,
+         next_ready ? gn_slot_ptr(gn_slot) : nullptr, rb.groups);
+    return next_ready;
 }
 
 // Small batches are launch-bound (141 launches, ~9 us of host work each, against ~5 us of GPU work): the second time the
@@ -594,7 +604,9 @@ void engine::run_direct(bool with_istft, stage_times * prof, int stop_stage) {
     launch_interp(ft, d_tok2_row0_, d_tok2_len_, fx, frm_.rows, dd, frm_.d_row_utt, frm_.d_row_pos, frm_.d_len, st_);
     if (stop(2, fx, dd, 0, 0, &frm_)) return;
     int gn_slot = 0;
-    for (const resblock & rb : mdl->prior) run_resblock(fx, fy, frm_, rb, gn_slot);
+    bool gn_ready = false;
+    for (size_t j = 0; j < mdl->prior.size(); ++j)
+        gn_ready = run_resblock(fx, fy, frm_, mdl->prior[j], gn_slot, gn_ready, j + 1 < mdl->prior.size());
     mark(2);
     if (stop(3, fx, dd, 0, 0, &frm_)) return;
 
@@ -612,7 +624,9 @@ void engine::run_direct(bool with_istft, stage_times * prof, int stop_stage) {
     if (stop(4, fx, dd, 0, 0, &frm_)) return;
 
     // ---- post ResNets, optional wave upsampler, iSTFT head (:1403-1461) ----
-    for (const resblock & rb : mdl->post) run_resblock(fx, fy, frm_, rb, gn_slot);
+    gn_ready = false;
+    for (size_t j = 0; j < mdl->post.size(); ++j)
+        gn_ready = run_resblock(fx, fy, frm_, mdl->post[j], gn_slot, gn_ready, j + 1 < mdl->post.size());
     if (stop(5, fx, dd, 0, 0, &frm_)) return;
     const seq_layout * cur = &frm_;
     int cur_c = dd;
@@ -624,7 +638,7 @@ void engine::run_direct(bool with_istft, stage_times * prof, int stop_stage) {
         launch_convt_fold_snake(ft, s.ksize * s.cout, cur->d_row0, cur->d_len, fy, nxt.rows, s.cout, s.ksize, s.factor,
                                 s.pad, s.up_bias, s.snake_a, s.snake_inv_b, nxt.d_row_utt, nxt.d_row_pos, st_);
         std::swap(fx, fy);
-        run_resblock(fx, fy, nxt, s.rb, gn_slot);
+        run_resblock(fx, fy, nxt, s.rb, gn_slot, false, false);
         cur = &nxt;
         cur_c = s.cout;
     }

@@ -107,7 +107,7 @@ private:
     const long long * d_audio_off_ = nullptr, * d_audio_len_ = nullptr;
 
     // workspace
-    dbuf xt_, fx_, fy_, ft_, act16_, qkv16_, att16_, ff16_, cond_, gn_stats_, gn_mr_, spec_buf_, audio_, peak_, pcm_;
+    dbuf xt_, fx_, fy_, ft_, act16_, qkv16_, att16_, ff16_, cond_, gn_stats_, spec_buf_, audio_, peak_, pcm_;
     int spec_pitch_ = 0;
     const void * dbg_ptr_ = nullptr; int dbg_cols_ = 0, dbg_is16_ = 0, dbg_dtype_ = 0; const seq_layout * dbg_lay_ = nullptr;
     float2 * rope_p_ = nullptr, * rope_d_ = nullptr; int rope_p_pos_ = 0, rope_d_pos_ = 0;
@@ -134,11 +134,14 @@ private:
 
     void gemm(const dbuf & a, const dev_linear & w, int M, int epilogue, void * out, int ldo, int out_dtype,
               const float * bias, const float * res, int ldr, const float * gate, const seq_layout * lay,
-              const float2 * rope = nullptr, int heads = 0);
+              const float2 * rope = nullptr, int heads = 0, double * gn_stats = nullptr, int gn_groups = 0);
     void run_tblock(float * x, const seq_layout & L, const tblock & blk, int dim, int heads, int ff, int window,
                     const float2 * rope, bool cond);
-    void run_resblock(float *& x, float *& y, const seq_layout & L, const resblock & rb, int & gn_slot);
-    void group_norm_silu(const float * x, const seq_layout & L, int channels, int groups, const dev_norm & n, int & gn_slot);
+    bool run_resblock(float *& x, float *& y, const seq_layout & L, const resblock & rb, int & gn_slot, bool in_ready,
+                      bool feeds_next);
+    void group_norm_silu(const float * x, const seq_layout & L, int channels, int groups, const dev_norm & n, int slot,
+                         bool stats_ready);
+    double * gn_slot_ptr(int slot) { return (double *) gn_stats_.p + (size_t) slot * n_utt_ * gn_groups_max_ * 2; }
 };
 
 // pinned result buffers handed to callers by the C API and returned through mio_tts_audio_free

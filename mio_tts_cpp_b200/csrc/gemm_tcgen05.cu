@@ -243,11 +243,13 @@ __device__ __forceinline__ float act_apply(float x, int act) {
 // fp32 box: out = act(acc + bias) * gate + residual, residual read from / result written to the same box slot.
 // BIAS/GATE/RES are compile-time so an absent term costs no issue slots.  The bias / gate values of the chunk (bv, gv)
 // were fetched by the caller one chunk ahead (zeros past N: those columns are clipped by the TMA store).
-template <bool BIAS, bool GATE, bool RES>
+// STATS: sq = {sum, sum of squares} of this row's columns 0-15 and 16-31 of the chunk (final values, residual included).
+template <bool BIAS, bool GATE, bool RES, bool STATS = false>
 __device__ __forceinline__ void chunk_store32(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, int lane,
-                                              const float4 (&bv)[8], const float4 (&gv)[8]) {
+                                              const float4 (&bv)[8], const float4 (&gv)[8], float (&sq)[4]) {
     const uint32_t row = buf + lane * 128;
     const uint32_t sw = (uint32_t) (lane & 7) << 4;
+    if (STATS) { sq[0] = sq[1] = sq[2] = sq[3] = 0.0f; }
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         const uint32_t addr = row + (((uint32_t) j << 4) ^ sw);
@@ -262,6 +264,10 @@ __device__ __forceinline__ void chunk_store32(const gemm_args & a, const uint32_
             const float4 q = lds128(addr);
             o.x += q.x; o.y += q.y; o.z += q.z; o.w += q.w;
         }
+        if (STATS) {
+            sq[2 * (j >> 2)] += (o.x + o.y) + (o.z + o.w);
+            sq[2 * (j >> 2) + 1] += (o.x * o.x + o.y * o.y) + (o.z * o.z + o.w * o.w);
+        }
         sts128(addr, o);
     }
 }
@@ -269,18 +275,23 @@ __device__ __forceinline__ void chunk_store32(const gemm_args & a, const uint32_
 // warp-uniform dispatch to the term combinations in use; has_res: the residual sits in the box and is added here
 // (false in reduce-add mode, where the box carries the new term alone)
 __device__ __forceinline__ void chunk_store32_any(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, int lane,
-                                                  const float4 (&bv)[8], const float4 (&gv)[8], bool has_res) {
+                                                  const float4 (&bv)[8], const float4 (&gv)[8], bool has_res, float (&sq)[4]) {
+    if (a.gn_stats) {   // the k=3 convolutions of the resnet blocks: bias, no gate; conv2 with the residual in the box
+        if (has_res) chunk_store32<true, false, true, true>(a, raw, buf, lane, bv, gv, sq);
+        else chunk_store32<true, false, false, true>(a, raw, buf, lane, bv, gv, sq);
+        return;
+    }
     if (a.gate) {
-        if (has_res) { if (a.bias) chunk_store32<true, true, true>(a, raw, buf, lane, bv, gv);
-                       else chunk_store32<false, true, true>(a, raw, buf, lane, bv, gv); }
-        else { if (a.bias) chunk_store32<true, true, false>(a, raw, buf, lane, bv, gv);
-               else chunk_store32<false, true, false>(a, raw, buf, lane, bv, gv); }
+        if (has_res) { if (a.bias) chunk_store32<true, true, true>(a, raw, buf, lane, bv, gv, sq);
+                       else chunk_store32<false, true, true>(a, raw, buf, lane, bv, gv, sq); }
+        else { if (a.bias) chunk_store32<true, true, false>(a, raw, buf, lane, bv, gv, sq);
+               else chunk_store32<false, true, false>(a, raw, buf, lane, bv, gv, sq); }
     } else if (has_res) {
-        if (a.bias) chunk_store32<true, false, true>(a, raw, buf, lane, bv, gv);
-        else chunk_store32<false, false, true>(a, raw, buf, lane, bv, gv);
+        if (a.bias) chunk_store32<true, false, true>(a, raw, buf, lane, bv, gv, sq);
+        else chunk_store32<false, false, true>(a, raw, buf, lane, bv, gv, sq);
     } else {
-        if (a.bias) chunk_store32<true, false, false>(a, raw, buf, lane, bv, gv);
-        else chunk_store32<false, false, false>(a, raw, buf, lane, bv, gv);
+        if (a.bias) chunk_store32<true, false, false>(a, raw, buf, lane, bv, gv, sq);
+        else chunk_store32<false, false, false>(a, raw, buf, lane, bv, gv, sq);
     }
 }
 
@@ -541,6 +552,7 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
         // STORE32 with a per-utterance gate: likewise this lane's row -> utterance index
         auto utt_of = [&](int w) {
             const int r = tile_row0(w) + lane;
+            if (a.gn_stats != nullptr) return (w < num_items && r < a.M) ? __ldg(a.row_utt + r) : -1;   // -1: not a data row
             return (a.gate != nullptr && a.row_utt != nullptr && w < num_items && r < a.M) ? __ldg(a.row_utt + r) : 0;
         };
         int utt_next = EPI == EPI_STORE32 ? utt_of(unit) : 0;
@@ -552,8 +564,10 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
             // rows this lane fetches for the transposed (cos,sin) staging (ROPE16: row (lane>>3)+4u, 16-byte slot lane&7)
             const float * gate_row = nullptr;
             const float4 * rope_row[EPI == EPI_ROPE16 ? 8 : 1];
+            int utt_row = 0;
             if constexpr (EPI == EPI_STORE32) {
                 if (a.gate) gate_row = a.gate + (size_t) max(utt_next, 0) * a.gate_ld;
+                utt_row = utt_next;
                 utt_next = utt_of(t + n_units);
             } else if constexpr (EPI == EPI_ROPE16) {
                 const int pos = max(pos_next, 0);
@@ -650,8 +664,35 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
                     if (has_res) mbar_wait(rbar(b), (nch / EPI_NBUF) & 1);       // residual box landed
                     else { if (lane == 0) bulk_wait_read<EPI_NBUF - 1>(); __syncwarp(); }
                     tmem_ld_wait();
-                    chunk_store32_any(a, raw, buf, lane, bv, gv, has_res);
+                    float sq[4];
+                    chunk_store32_any(a, raw, buf, lane, bv, gv, has_res, sq);
                     bg_fetch(c + EW);
+                    if (a.gn_stats != nullptr) {
+                        // GroupNorm statistics of the consumer: this row's two 16-column halves of the chunk
+                        const int cpg = a.N / a.gn_groups;                       // 16, or a multiple of 32
+                        const int g0 = n / cpg, g1 = (n + 16) / cpg;
+                        if (g0 == g1) { sq[0] += sq[2]; sq[1] += sq[3]; }
+                        const int u0 = __shfl_sync(0xffffffffu, utt_row, 0);
+                        if (__all_sync(0xffffffffu, utt_row == u0 && u0 >= 0)) {  // one utterance: reduce over the 32 rows first
+                            // in DOUBLE: which rows share a warp depends on where the utterance sits in the batch layout, and
+                            // an utterance must decode to the same bits alone and inside any batch -- fp32 partial sums over
+                            // rows would make the statistics depend on that grouping
+                            double d[4] = {(double) sq[0], (double) sq[1], (double) sq[2], (double) sq[3]};
+#pragma unroll
+                            for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+                                for (int e = 0; e < 4; ++e) d[e] += __shfl_xor_sync(0xffffffffu, d[e], o);
+                            }
+                            const double dv = lane == 0 ? d[0] : (lane == 1 ? d[1] : (lane == 2 ? d[2] : d[3]));
+                            if (lane < 4 && (lane < 2 || g0 != g1))
+                                atomicAdd(a.gn_stats + ((size_t) u0 * a.gn_groups + (lane < 2 ? g0 : g1)) * 2 + (lane & 1), dv);
+                        } else if (utt_row >= 0) {                                // utterance boundary or gap rows in the warp
+                            double * sp = a.gn_stats + (size_t) utt_row * a.gn_groups * 2;
+                            atomicAdd(sp + 2 * g0, (double) sq[0]);
+                            atomicAdd(sp + 2 * g0 + 1, (double) sq[1]);
+                            if (g0 != g1) { atomicAdd(sp + 2 * g1, (double) sq[2]); atomicAdd(sp + 2 * g1 + 1, (double) sq[3]); }
+                        }
+                    }
                 }
                 fence_proxy_async();
                 __syncwarp();
@@ -830,7 +871,11 @@ void gemm_launch(const gemm_args & a, int num_sms, cudaStream_t st) {
         ncta = (c && std::atoi(c) == 1) ? 1 : 2;
     }
     gemm_args g = a;
-    g.red_add = (use_red && a.res != nullptr && a.epilogue == EPI_STORE32) ? 1 : 0;
+    if (g.gn_stats != nullptr && (a.epilogue != EPI_STORE32 || a.row_utt == nullptr || a.bias == nullptr || a.gate != nullptr ||
+                                  !gemm_gn_stats_ok(a.N, a.gn_groups)))
+        throw cuda_error("gemm: GroupNorm statistics need the fp32-store epilogue with bias, row_utt, no gate, and a supported group width");
+    // the statistics are taken over the FINAL values, so the residual has to pass through the SM (no L2 reduce-add)
+    g.red_add = (use_red && a.res != nullptr && a.epilogue == EPI_STORE32 && g.gn_stats == nullptr) ? 1 : 0;
     if (gemm_block_n(a.N) == 256) {
         if (ncta == 2) { if (ew == 1) launch_bn<256, 1, 2>(g, num_sms, st); else launch_bn<256, 2, 2>(g, num_sms, st); }
         else { if (ew == 1) launch_bn<256, 1, 1>(g, num_sms, st); else launch_bn<256, 2, 1>(g, num_sms, st); }

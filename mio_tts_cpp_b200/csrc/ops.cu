@@ -295,22 +295,22 @@ __global__ void gn_stats_kernel(const float * __restrict__ x, int dim, int group
         atomicAdd(&stats[(size_t) t.utt * groups * 2 + i], s_acc[i]);
 }
 
-__global__ void gn_finalize_kernel(const double * __restrict__ stats, const int * __restrict__ utt_len, int cpg,
-                                   int groups, int n_utt, float eps, float2 * __restrict__ mr) {
-    MIO_PDL_PROLOGUE();
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_utt * groups) return;
-    const double n = (double) utt_len[i / groups] * (double) cpg;
-    const double mean = stats[2 * i] / n;
-    double var = stats[2 * i + 1] / n - mean * mean;
+// (sum, sumsq) of one (utterance, group) -> (mean, rstd); the arithmetic of ggml_group_norm's tail in double
+__device__ __forceinline__ float2 gn_mean_rstd(const double * __restrict__ stats, const int * __restrict__ utt_len, int utt,
+                                               int groups, int g, int cpg, float eps) {
+    const double n = (double) __ldg(utt_len + utt) * (double) cpg;
+    const double * sp = stats + ((size_t) utt * groups + g) * 2;
+    const double mean = sp[0] / n;
+    double var = sp[1] / n - mean * mean;
     if (var < 0.0) var = 0.0;
-    mr[i] = make_float2((float) mean, 1.0f / sqrtf((float) var + eps));
+    return make_float2((float) mean, 1.0f / sqrtf((float) var + eps));
 }
 
 // ---- GroupNorm phase 2: normalise, affine, SiLU, round to the conv operand type (fp16, as the reference's
 //      im2col does: llama.cpp/ggml/src/ggml.c:4409-4426), zero the layout's gap rows. ----
 __global__ void gn_apply_kernel(const float * __restrict__ x, int rows, int dim, int groups,
-                                const float2 * __restrict__ mr, const float * __restrict__ w,
+                                const double * __restrict__ stats, const int * __restrict__ utt_len, float eps,
+                                const float * __restrict__ w,
                                 const float * __restrict__ b, const int * __restrict__ row_utt, void * out16,
                                 int out_dtype) {
     MIO_PDL_PROLOGUE();
@@ -331,7 +331,7 @@ __global__ void gn_apply_kernel(const float * __restrict__ x, int rows, int dim,
         const float bv[4] = {bb.x, bb.y, bb.z, bb.w};
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const float2 m = __ldg(mr + (size_t) utt * groups + (c4 * 4 + k) / cpg);
+            const float2 m = gn_mean_rstd(stats, utt_len, utt, groups, (c4 * 4 + k) / cpg, cpg, eps);
             const float t = ((y[k] - m.x) * m.y) * wv[k] + bv[k];
             y[k] = silu_exact(t);
         }
@@ -345,7 +345,8 @@ __global__ void gn_apply_kernel(const float * __restrict__ x, int rows, int dim,
 // its channel quad (affine weights in registers) and walks rows; SiLU on the SFU (output is rounded to fp16 anyway)
 template <int ROWS_PER_THREAD>
 __global__ void gn_apply_fast_kernel(const float * __restrict__ x, int rows, int dim, int groups,
-                                     const float2 * __restrict__ mr, const float * __restrict__ w,
+                                     const double * __restrict__ stats, const int * __restrict__ utt_len, float eps,
+                                     const float * __restrict__ w,
                                      const float * __restrict__ b, const int * __restrict__ row_utt, void * out16,
                                      int out_dtype) {
     MIO_PDL_PROLOGUE();
@@ -364,13 +365,15 @@ __global__ void gn_apply_fast_kernel(const float * __restrict__ x, int rows, int
         utt[it] = row < rows ? __ldg(row_utt + row) : -1;
         if (utt[it] >= 0) v[it] = reinterpret_cast<const float4 *>(x)[(size_t) row * c4n + c4];
     }
+    int m_utt = -1;                 // the thread's rows almost always share one utterance: (mean, rstd) derived once
+    float2 m = make_float2(0.f, 1.f);
 #pragma unroll
     for (int it = 0; it < ROWS_PER_THREAD; ++it) {
         const int row = row_base + it * rpb;
         if (row >= rows) continue;
         uint2 o = make_uint2(0u, 0u);
         if (utt[it] >= 0) {
-            const float2 m = __ldg(mr + (size_t) utt[it] * groups + g);
+            if (utt[it] != m_utt) { m_utt = utt[it]; m = gn_mean_rstd(stats, utt_len, m_utt, groups, g, dim / groups, eps); }
             float y[4] = {v[it].x, v[it].y, v[it].z, v[it].w};
             const float wv[4] = {ww.x, ww.y, ww.z, ww.w};
             const float bv[4] = {bb.x, bb.y, bb.z, bb.w};
@@ -564,8 +567,8 @@ void launch_gn_stats(const float * x, int dim, int groups, const row_tile * tile
     count_launch();
 }
 
-void launch_gn_apply(const float * x, int rows, int dim, int groups, const float2 * mean_rstd, const float * w,
-                     const float * b, const int * row_utt, void * out16, int out_dtype, cudaStream_t st) {
+void launch_gn_apply(const float * x, int rows, int dim, int groups, const double * stats, const int * utt_len, float eps,
+                     const float * w, const float * b, const int * row_utt, void * out16, int out_dtype, cudaStream_t st) {
     if (rows <= 0) return;
     if (dim & 3) throw cuda_error("group norm: channel count must be a multiple of 4");
     const int c4n = dim >> 2, cpg = dim / groups;
@@ -573,19 +576,11 @@ void launch_gn_apply(const float * x, int rows, int dim, int groups, const float
         constexpr int RPT = 4;
         const int rows_per_block = (256 / c4n) * RPT;
         launch_pdl(gn_apply_fast_kernel<RPT>, dim3(blocks_for((size_t) rows, rows_per_block)), dim3(256), 0, st, 
-            x, rows, dim, groups, mean_rstd, w, b, row_utt, out16, out_dtype);
+            x, rows, dim, groups, stats, utt_len, eps, w, b, row_utt, out16, out_dtype);
     } else {
         launch_pdl(gn_apply_kernel, dim3(blocks_for((size_t) rows * (dim >> 2), 256)), dim3(256), 0, st, 
-            x, rows, dim, groups, mean_rstd, w, b, row_utt, out16, out_dtype);
+            x, rows, dim, groups, stats, utt_len, eps, w, b, row_utt, out16, out_dtype);
     }
-    MIO_CUDA(cudaGetLastError());
-    count_launch();
-}
-
-void launch_gn_finalize(const double * stats, const int * utt_len, int cpg, int groups, int n_utt, float eps,
-                        float2 * mr, cudaStream_t st) {
-    launch_pdl(gn_finalize_kernel, dim3(blocks_for((size_t) n_utt * groups, 128)), dim3(128), 0, st, stats, utt_len, cpg, groups, n_utt,
-                                                                               eps, mr);
     MIO_CUDA(cudaGetLastError());
     count_launch();
 }
