@@ -152,6 +152,11 @@ void launch_snake(float * x, int rows, int dim, const float * snake_a, const flo
 // ---------------------------------------------------------------------------------------------
 void launch_attention(const void * qkv16, void * out16, int dtype, int dim, int heads, int window,
                       const row_tile * tiles, int n_tiles, bool force_generic, cudaStream_t st);
+// persistent TMA-fed form (head_dim 64, window <= 65): map_qkv = make_tmap_16(qkv, rows, 3*dim, 64),
+// map_out = make_tmap_16(out, rows, dim, 16); same tiles as launch_attention
+bool attention_tma_ok(int dim, int heads, int window);
+void launch_attention_tma(const CUtensorMap & map_qkv, const CUtensorMap & map_out, void * out16, int dtype, int dim, int heads,
+                          int window, int rows, const row_tile * tiles, int n_tiles, int num_sms, cudaStream_t st);
 
 // ---------------------------------------------------------------------------------------------
 // iSTFT (istft.cu)

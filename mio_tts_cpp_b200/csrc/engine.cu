@@ -159,6 +159,16 @@ const CUtensorMap & engine::amap(const dbuf & b, int K) {
     return ins.first->second;
 }
 
+// 16-bit [rows, cols] map with a 64-column x box_rows box (the attention kernel's q/k/v loads and output stores)
+const CUtensorMap & engine::xmap(const void * p, int rows, int cols, int box_rows) {
+    const std::array<uint64_t, 5> key = {(uint64_t) (uintptr_t) p, (uint64_t) rows, (uint64_t) cols, (uint64_t) box_rows, 16};
+    auto it = omaps_.find(key);
+    if (it != omaps_.end()) return it->second;
+    if (omaps_.size() > 512) omaps_.clear();
+    auto ins = omaps_.emplace(key, make_tmap_16(p, (uint64_t) rows, (uint64_t) cols, (uint32_t) box_rows));
+    return ins.first->second;
+}
+
 const CUtensorMap & engine::omap(const void * p, int rows, int cols, int ld, int elem_bytes) {
     const std::array<uint64_t, 5> key = {(uint64_t) (uintptr_t) p, (uint64_t) rows, (uint64_t) cols, (uint64_t) ld,
                                          (uint64_t) elem_bytes};
@@ -450,7 +460,11 @@ void engine::run_tblock(float * x, const seq_layout & L, const tblock & blk, int
         while (gemm_ev_.size() < evi + 2) { cudaEvent_t e; MIO_CUDA(cudaEventCreate(&e)); gemm_ev_.push_back(e); }
         MIO_CUDA(cudaEventRecord(gemm_ev_[evi], st_));
     }
-    launch_attention(qkv16_.p, att16_.p, ldt, dim, heads, window, L.d_tiles, L.n_tiles, force_generic_attention, st_);
+    if (!force_generic_attention && attention_tma_ok(dim, heads, window))
+        launch_attention_tma(xmap(qkv16_.p, rows, 3 * dim, 64), xmap(att16_.p, rows, dim, 16), att16_.p, ldt, dim, heads, window,
+                             rows, L.d_tiles, L.n_tiles, mdl->num_sms, st_);
+    else
+        launch_attention(qkv16_.p, att16_.p, ldt, dim, heads, window, L.d_tiles, L.n_tiles, force_generic_attention, st_);
     if (prof_gemm_) { MIO_CUDA(cudaEventRecord(gemm_ev_[evi + 1], st_)); attn_ev_.push_back(evi); }
     gemm(att16_, blk.o, rows, EPI_STORE32, x, dim, 0, nullptr, x, dim, cond ? cv + blk.cond_attn_off + 2 * dim : nullptr, &L);
     if (cond)

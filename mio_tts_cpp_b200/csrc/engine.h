@@ -112,6 +112,7 @@ private:
     const void * dbg_ptr_ = nullptr; int dbg_cols_ = 0, dbg_is16_ = 0, dbg_dtype_ = 0; const seq_layout * dbg_lay_ = nullptr;
     float2 * rope_p_ = nullptr, * rope_d_ = nullptr; int rope_p_pos_ = 0, rope_d_pos_ = 0;
     std::map<std::pair<const void *, int>, CUtensorMap> tmaps_;
+    const CUtensorMap & xmap(const void * p, int rows, int cols, int box_rows);
     std::map<std::array<uint64_t, 5>, CUtensorMap> omaps_;   // (ptr, rows, cols, ld, elem bytes) -> output map
     std::map<std::pair<int, int>, istft_plan> istft_plans_;
 

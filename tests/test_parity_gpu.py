@@ -442,3 +442,33 @@ def test_pipelined_halves_match_single_calls(ctxs, emb):
         m.synthesize_batch(bad, embs)
     b, _ = m.synthesize_batch(codes, embs)
     assert all(x.tobytes() == y.tobytes() for x, y in zip(a, b))
+
+
+def test_attention_tma_kernel_is_bit_identical_to_the_first_version(gguf_paths, emb):
+    """The persistent TMA-fed band kernel and the one-tile-per-CTA cp.async kernel (MIO_TTS_B200_ATTN=v1) run the same
+    MMAs in the same order on the same fragments: spectrograms must agree bit for bit (full tiles through the TMA store,
+    partial last tiles through the plain stores, ragged batch)."""
+    code = (
+        "import sys, hashlib, numpy as np; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "from mio_tts_cpp_b200 import MioTTS\n"
+        "emb = np.load(%r); rng = np.random.default_rng(5); h = hashlib.sha256()\n"
+        "for path in %r:\n"
+        "    m = MioTTS(path)\n"
+        "    for T in (1, 37, 64, 65, 400):\n"
+        "        h.update(m.decode_spec(rng.integers(0, 12800, T).astype(np.int32), emb).tobytes())\n"
+        "    codes = [rng.integers(0, 12800, int(t)).astype(np.int32) for t in rng.integers(1, 300, 20)]\n"
+        "    for a in m.synthesize_batch(codes, [emb] * len(codes))[0]: h.update(np.asarray(a).tobytes())\n"
+        "    m.free()\n"
+        "print('HASH', h.hexdigest())\n"
+    ) % (ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "tests", "golden", "en_female_emb.npy"),
+         [gguf_paths("tiny")[0], gguf_paths("default")[0]])
+    hashes = {}
+    for mode in ("v1", None):
+        env = dict(os.environ)
+        env.pop("MIO_TTS_B200_ATTN", None)
+        if mode is not None:
+            env["MIO_TTS_B200_ATTN"] = mode
+        out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+        assert out.returncode == 0, out.stderr[-2000:]
+        hashes[mode] = [ln for ln in out.stdout.splitlines() if ln.startswith("HASH")][-1].split()[1]
+    assert len(set(hashes.values())) == 1, hashes
