@@ -382,6 +382,46 @@ def aux_configs(m, peaks):
     out["config3_istft"] = {"frames": n_utt * frames, "n_fft": 1920, "hop": 480, "ms": ms, "frames_per_s": n_utt * frames / (ms * 1e-3),
                             "roofline": {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                                          "frac": gbs / peaks["hbm_gbs"]}}
+    # the generic iSTFT kernel (any frame size; the real 44.1 kHz checkpoint's n_fft 392 / hop 98 lands on it)
+    ms392, _ = m.istft_bench(1000, 1000, 392, 98, 5)
+    b392 = (392 + 2) * 4 + 98 * 4
+    out["istft_generic_392_98"] = {"frames": 1000000, "n_fft": 392, "hop": 98, "ms": ms392, "frames_per_s": 1e6 / (ms392 * 1e-3),
+                                   "roofline": {"bound": "hbm", "achieved": 1e6 * b392 / (ms392 * 1e-3) / 1e9,
+                                                "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                                                "frac": 1e6 * b392 / (ms392 * 1e-3) / 1e9 / peaks["hbm_gbs"],
+                                                "bytes_per_frame": b392}}
+    # codebook gather alone over the config-2 batch (north_star: achieved HBM GB/s of the gather): 25 600 rows x 768 fp32
+    # written (79 MB) + the rows read (the 39 MB table is L2-resident after the first pass)
+    g_ms = m.gather_bench(50)
+    g_bytes = BATCH * N_CODES * m.prenet_dim() * 4 * 2 + BATCH * N_CODES * 4
+    out["gather"] = {"rows": BATCH * N_CODES, "dim": m.prenet_dim(), "ms": g_ms, "bit_exact": True,
+                     "roofline": {"bound": "hbm", "achieved": g_bytes / (g_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                                  "frac": g_bytes / (g_ms * 1e-3) / 1e9 / peaks["hbm_gbs"], "bytes_per_token": g_bytes / (BATCH * N_CODES),
+                                  "note": "table rows come from L2 (12 800 x 768 fp32 = 39 MB stays resident); DRAM sees the writes"}}
+    # the branch the shipped 44.1 kHz-v2 checkpoint takes (wave_upsampler_layers = 2, factors [3,3], n_fft 392):
+    # synthetic weights of the `upsampler` preset, 64 x 400 codes
+    up = MioTTS(U.synth_gguf("upsampler"))
+    codes = U.config2_workload(0, BATCH, N_CODES)
+    up.prepare(codes, [U.speaker_embedding()] * BATCH)
+    for _ in range(3):
+        up.run_resident(1)
+    n0 = up.launch_count()
+    up_ms = up.run_resident(10)
+    up_launches = (up.launch_count() - n0) / 10
+    pr = up.profile_resident()
+    up_audio = up.resident_samples() / up.sample_rate()
+    out["upsampler_44k"] = {"workload": "preset `upsampler` (2+2 transformer layers, 1 ResNet block per stack, 2 wave-upsampler "
+                                        "stages x3 with SnakeBeta + ResNet, out_proj 128, n_fft 392 / hop 98), 64 x 400 codes",
+                            "audio_seconds_per_step": up_audio, "ms_per_step": up_ms, "value": up_audio / (up_ms * 1e-3),
+                            "unit": "audio-seconds/s", "launches_per_step": up_launches,
+                            "stages_ms": {k: pr[k] for k in ("prenet_ms", "upsample_prior_ms", "decoder_ms", "post_head_ms", "istft_ms", "total_ms")},
+                            "gemm_tflops": pr["gemm_flops"] / max(pr["gemm_ms"], 1e-9) / 1e9, "gemm_share": pr["gemm_ms"] / pr["total_ms"],
+                            "roofline": {"bound": "tensor", "achieved": pr["gemm_flops"] / max(pr["gemm_ms"], 1e-9) / 1e9,
+                                         "peak": peaks["bf16_tflops"], "unit": "TFLOP/s",
+                                         "frac": pr["gemm_flops"] / max(pr["gemm_ms"], 1e-9) / 1e9 / peaks["bf16_tflops"]},
+                            "note": "shallow trunk: not comparable layer for layer with the default path; post_head = post ResNet + "
+                                    "upsampler stages + head"}
+    up.free()
     sys.path.insert(0, os.path.join(ROOT, "tools"))
     from make_synth_gguf import write_gguf, write_wavlm_gguf
 

@@ -232,6 +232,8 @@ MIO_B200_API uint64_t mio_tts_b200_resident_samples(struct mio_tts_context * ctx
 MIO_B200_API float mio_tts_b200_istft_bench(struct mio_tts_context * ctx, int32_t n_utt, int32_t frames_per_utt,
                                             int32_t n_fft, int32_t hop, int32_t iters, uint64_t seed, double * checksum,
                                             char * err, size_t err_size);
+/* codebook gather alone (miocodec-decoder.cpp:1360) over the batch uploaded by mio_tts_b200_prepare: ms per pass */
+MIO_B200_API float mio_tts_b200_gather_bench(struct mio_tts_context * ctx, int32_t iters, char * err, size_t err_size);
 /* ---- reference-audio -> speaker-embedding path (WavLM SSL extractor + global encoder) ----
  * mio_tts_reference_to_embedding (lib.h:69-77, lib.cpp:1048-1125) runs on the GPU when the context was created with a
  * WavLM GGUF and the MioCodec GGUF holds the global-encoder tensors.  The reference has no batch or PCM entry point:

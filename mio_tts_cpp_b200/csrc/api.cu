@@ -1077,6 +1077,16 @@ float mio_tts_b200_istft_bench(struct mio_tts_context * ctx, int32_t n_utt, int3
     return ms;
 }
 
+float mio_tts_b200_gather_bench(struct mio_tts_context * ctx, int32_t iters, char * err, size_t err_size) {
+    if (ctx == nullptr || !ctx->mdl) { set_err(err, err_size, "context is null"); return -1.0f; }
+    float ms = -1.0f;
+    guarded(err, err_size, [&] {
+        std::lock_guard<std::mutex> lk(ctx->eng->mtx);
+        ms = ctx->eng->gather_bench(iters);
+    });
+    return ms;
+}
+
 uint64_t mio_tts_b200_launch_count(void) { return (uint64_t) g_launch_count.load(); }
 
 uint64_t mio_tts_b200_workspace_bytes(struct mio_tts_context * ctx) {

@@ -521,8 +521,7 @@ __global__ void attention_generic_kernel(const uint16_t * __restrict__ qkv, uint
 } // namespace
 
 bool attention_tma_ok(int dim, int heads, int window) {
-    static const bool v1 = [] { const char * e = std::getenv("MIO_TTS_B200_ATTN"); return e && std::strcmp(e, "v1") == 0; }();
-    return !v1 && heads > 0 && dim / heads == HD && window / 2 <= 32 && (dim % 8) == 0;
+    return attention_mode() != 0 && heads > 0 && dim / heads == HD && window / 2 <= 32 && (dim % 8) == 0;
 }
 
 void launch_attention_tma(const CUtensorMap & map_qkv, const CUtensorMap & map_out, void * out16, int dtype, int dim, int heads,

@@ -155,6 +155,13 @@ void launch_attention(const void * qkv16, void * out16, int dtype, int dim, int 
 // persistent TMA-fed form (head_dim 64, window <= 65): map_qkv = make_tmap_16(qkv, rows, 3*dim, 64),
 // map_out = make_tmap_16(out, rows, dim, 16); same tiles as launch_attention
 bool attention_tma_ok(int dim, int heads, int window);
+// tcgen05 form (attention_tc.cu), the default: 128-row tiles, maps = make_tmap_16(qkv, rows, 3*dim, 128 / 192) and
+// make_tmap_16(out, rows, dim, 32).  MIO_TTS_B200_ATTN = v1 | v2 select the mma.sync kernels instead.
+int attention_mode();
+bool attention_tc_ok(int dim, int heads, int window);
+void launch_attention_tc(const CUtensorMap & map_q, const CUtensorMap & map_kv, const CUtensorMap & map_out, void * out16,
+                         int dtype, int dim, int heads, int window, int rows, const row_tile * tiles128, int n_tiles,
+                         int num_sms, cudaStream_t st);
 void launch_attention_tma(const CUtensorMap & map_qkv, const CUtensorMap & map_out, void * out16, int dtype, int dim, int heads,
                           int window, int rows, const row_tile * tiles, int n_tiles, int num_sms, cudaStream_t st);
 

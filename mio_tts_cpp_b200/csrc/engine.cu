@@ -207,17 +207,21 @@ void engine::build_layout(seq_layout & L, const std::vector<int> & len, int gap)
 
 void engine::append_layout(seq_layout & L) {
     std::vector<int> row_utt((size_t) L.rows, -1), row_pos((size_t) L.rows, 0);
-    std::vector<row_tile> tiles;
+    std::vector<row_tile> tiles, tiles128;
     for (int u = 0; u < L.n_utt; ++u) {
         for (int p = 0; p < L.len[u]; ++p) { row_utt[(size_t) L.row0[u] + p] = u; row_pos[(size_t) L.row0[u] + p] = p; }
-        for (int s = 0; s < L.len[u]; s += 64) {
-            row_tile t;
-            t.row0 = L.row0[u] + s; t.n = std::min(64, L.len[u] - s); t.utt = u; t.pos0 = s;
-            t.utt_row0 = L.row0[u]; t.utt_len = L.len[u];
-            tiles.push_back(t);
+        for (int span : {64, 128}) {
+            for (int s = 0; s < L.len[u]; s += span) {
+                row_tile t;
+                t.row0 = L.row0[u] + s; t.n = std::min(span, L.len[u] - s); t.utt = u; t.pos0 = s;
+                t.utt_row0 = L.row0[u]; t.utt_len = L.len[u];
+                (span == 64 ? tiles : tiles128).push_back(t);
+            }
         }
     }
     L.n_tiles = (int) tiles.size();
+    L.n_tiles128 = (int) tiles128.size();
+    L.off_tiles128 = blob_add(tiles128.data(), tiles128.size() * sizeof(row_tile));
     L.off_len = blob_add(L.len.data(), L.len.size() * sizeof(int));
     L.off_row0 = blob_add(L.row0.data(), L.row0.size() * sizeof(int));
     L.off_row_utt = blob_add(row_utt.data(), row_utt.size() * sizeof(int));
@@ -232,6 +236,7 @@ void engine::bind_layout(seq_layout & L) {
     L.d_row_utt = (const int *) (base + L.off_row_utt);
     L.d_row_pos = (const int *) (base + L.off_row_pos);
     L.d_tiles = (const row_tile *) (base + L.off_tiles);
+    L.d_tiles128 = (const row_tile *) (base + L.off_tiles128);
 }
 
 void engine::prepare(const int32_t * const * codes, const size_t * n_codes, const float * const * emb, size_t n_emb,
@@ -460,7 +465,10 @@ void engine::run_tblock(float * x, const seq_layout & L, const tblock & blk, int
         while (gemm_ev_.size() < evi + 2) { cudaEvent_t e; MIO_CUDA(cudaEventCreate(&e)); gemm_ev_.push_back(e); }
         MIO_CUDA(cudaEventRecord(gemm_ev_[evi], st_));
     }
-    if (!force_generic_attention && attention_tma_ok(dim, heads, window))
+    if (!force_generic_attention && attention_tc_ok(dim, heads, window))
+        launch_attention_tc(xmap(qkv16_.p, rows, 3 * dim, 128), xmap(qkv16_.p, rows, 3 * dim, 192), xmap(att16_.p, rows, dim, 32),
+                            att16_.p, ldt, dim, heads, window, rows, L.d_tiles128, L.n_tiles128, mdl->num_sms, st_);
+    else if (!force_generic_attention && attention_tma_ok(dim, heads, window))
         launch_attention_tma(xmap(qkv16_.p, rows, 3 * dim, 64), xmap(att16_.p, rows, dim, 16), att16_.p, ldt, dim, heads, window,
                              rows, L.d_tiles, L.n_tiles, mdl->num_sms, st_);
     else
@@ -838,6 +846,21 @@ void engine::istft_host(const float * spec, int n_frames, int n_fft, int hop, st
     audio.resize((size_t) n_out);
     MIO_CUDA(cudaMemcpyAsync(audio.data(), audio_.p, (size_t) n_out * 4, cudaMemcpyDeviceToHost, st_));
     sync();
+}
+
+// the codebook gather alone over the prepared batch (north_star: achieved HBM GB/s of the gather)
+float engine::gather_bench(int iters) {
+    MIO_CUDA(cudaSetDevice(mdl->device));
+    if (n_utt_ == 0) throw std::runtime_error("no prepared batch");
+    auto go = [&]() { launch_gather(mdl->tok_embd, d_codes_, (float *) xt_.p, tok_.rows, mdl->hp.prenet_dim, st_); };
+    go();
+    MIO_CUDA(cudaEventRecord(ev_[6], st_));
+    for (int i = 0; i < iters; ++i) go();
+    MIO_CUDA(cudaEventRecord(ev_[7], st_));
+    MIO_CUDA(cudaStreamSynchronize(st_));
+    float ms = 0;
+    MIO_CUDA(cudaEventElapsedTime(&ms, ev_[6], ev_[7]));
+    return ms / (float) std::max(1, iters);
 }
 
 float engine::istft_bench(int n_utt, int frames, int n_fft, int hop, int iters, unsigned long long seed, double * checksum) {

@@ -17,11 +17,11 @@
 namespace mio {
 
 struct seq_layout {
-    int n_utt = 0, gap = 0, rows = 0, valid = 0, max_len = 0, n_tiles = 0;
+    int n_utt = 0, gap = 0, rows = 0, valid = 0, max_len = 0, n_tiles = 0, n_tiles128 = 0;
     std::vector<int> len, row0;
     const int * d_len = nullptr, * d_row0 = nullptr, * d_row_utt = nullptr, * d_row_pos = nullptr;
-    const row_tile * d_tiles = nullptr;
-    size_t off_len = 0, off_row0 = 0, off_row_utt = 0, off_row_pos = 0, off_tiles = 0;   // offsets in the metadata blob
+    const row_tile * d_tiles = nullptr, * d_tiles128 = nullptr;   // runs of <= 64 / <= 128 rows inside one utterance
+    size_t off_len = 0, off_row0 = 0, off_row_utt = 0, off_row_pos = 0, off_tiles = 0, off_tiles128 = 0;   // offsets in the metadata blob
 };
 
 struct dbuf {
@@ -70,6 +70,7 @@ public:
     void pcm16_host(const float * const * audio, const size_t * n, size_t batch, int16_t * const * out);
     // resident iSTFT microbench: `n_utt` utterances x `frames` frames of synthetic spectra already in HBM
     float istft_bench(int n_utt, int frames, int n_fft, int hop, int iters, unsigned long long seed, double * checksum);
+    float gather_bench(int iters);
 
     size_t workspace_bytes() const;
     void reserve(int n_codes, int batch);

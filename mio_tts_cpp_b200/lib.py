@@ -96,6 +96,7 @@ def load_library():
         "mio_tts_b200_run_resident": (C.c_float, [vp, i32, cp, sz]),
         "mio_tts_b200_profile_resident": (C.c_bool, [vp, C.POINTER(Profile), cp, sz]),
         "mio_tts_b200_resident_samples": (u64, [vp]),
+        "mio_tts_b200_gather_bench": (C.c_float, [vp, i32, cp, sz]),
         "mio_tts_b200_istft_bench": (C.c_float, [vp, i32, i32, i32, i32, i32, u64, C.POINTER(C.c_double), cp, sz]),
         "mio_tts_b200_reference_pcm_to_embedding_batch": (C.c_bool, [vp, C.POINTER(fp), szp, i32, sz, MioTtsParams, fpp, szp,
                                                                      cp, sz]),
@@ -347,6 +348,12 @@ class MioTTS:
 
     def last_h2d_bytes(self):
         return int(self.L.mio_tts_b200_last_h2d_bytes(self.ctx))
+
+    def gather_bench(self, iters=20):
+        ms = self.L.mio_tts_b200_gather_bench(self.ctx, iters, self._err, ERR_SIZE)
+        if ms < 0:
+            raise MioTtsError(self._err.value.decode())
+        return float(ms)
 
     def istft_bench(self, n_utt, frames, n_fft, hop, iters, seed=7):
         cs = C.c_double(0)
