@@ -37,7 +37,7 @@ constexpr int AT_STAGES = 3;
 constexpr int AT_Q_BYTES = AT_Q * 128, AT_KV_BYTES = AT_K * 128;
 constexpr int AT_STAGE_BYTES = AT_Q_BYTES + 2 * AT_KV_BYTES;        // 64 KB
 constexpr int AT_OUT_WARP_BYTES = 32 * 128;                         // one warp's 32 x 64 output box
-constexpr int AT_THREADS = 384;                                     // warp 0 TMA, warp 1 MMA, warps 4-7 / 8-11 softmax sets
+constexpr int AT_THREADS = 640;                                     // warp 0 TMA, warp 1 MMA, warps 4-11 / 12-19 softmax sets
 constexpr int AT_SMEM_BYTES = AT_STAGES * AT_STAGE_BYTES + 8 * AT_OUT_WARP_BYTES + 256 + 1024;
 constexpr int AT_TMEM_COLS = 512;                                   // two sets x (S 192 + O 64)
 
@@ -107,6 +107,29 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
         : "r"(taddr)
         : "memory");
 }
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&r)[8]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                 ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_st1(uint32_t taddr, uint32_t v) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(taddr), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t tmem_ld1(uint32_t taddr) {     // completes before returning
+    uint32_t v;
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(v) : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+    return v;
+}
 __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
     asm volatile(
         "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
@@ -160,7 +183,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attention_band_tc_kernel(const 
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < AT_STAGES; ++s) { bar_init(load_full(s), 1); bar_init(load_empty(s), 1); }
-        for (int b = 0; b < 2; ++b) { bar_init(s_full(b), 1); bar_init(p_full(b), 4); bar_init(o_full(b), 1); }
+        for (int b = 0; b < 2; ++b) { bar_init(s_full(b), 1); bar_init(p_full(b), 8); bar_init(o_full(b), 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -247,10 +270,17 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attention_band_tc_kernel(const 
             }
         }
     } else if (warp >= 4) {
-        // ===== softmax / output warps =====
-        const int set = (warp - 4) >> 2, quad = warp & 3;
+        // ===== softmax / output warps: two sets (alternate items) x two halves x four TMEM lane quadrants =====
+        // A query row is shared by TWO threads (same lane of warps `quad` of the two halves): half h owns score columns
+        // idx [48h, 48h+48) of the 96 its quadrant can see, P words [24h, 24h+24) of the quadrant's 48, and output columns
+        // [32h, 32h+32).  Row max and row sum cross the pair through four spare TMEM columns of the row's own lane (the
+        // set's O columns, idle until the PV MMAs that this pair's p_full arrivals release) and a 64-thread named barrier.
+        // Sixteen softmax warps (four per scheduler) hide the TMEM / MUFU / barrier latencies that eight could not.
+        const int cw = warp - 4;
+        const int set = cw >> 3, half = (cw >> 2) & 1, quad = warp & 3;
+        const int pair_bar = 1 + set * 4 + quad;                       // named barrier of the two warps sharing these rows
         const int hw = a.half_window;
-        const uint32_t obuf = out_base + (warp - 4) * AT_OUT_WARP_BYTES;
+        const uint32_t obuf = out_base + (set * 4 + quad) * AT_OUT_WARP_BYTES;
         const uint32_t lane_addr = (uint32_t) (quad * 32) << 16;
         const int gstep_t = (2 * (int) gridDim.x) / a.heads, gstep_h = (2 * (int) gridDim.x) % a.heads;
         int tile, head;
@@ -258,6 +288,12 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attention_band_tc_kernel(const 
             const int item = (int) blockIdx.x + set * (int) gridDim.x;
             tile = item / a.heads; head = item % a.heads;
         }
+        // (tcgen05 accesses of the two warps are ordered across the barrier by the before / after thread-sync fences)
+        auto pair_sync = [&]() {
+            fence_before();
+            asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+            fence_after();
+        };
         bool store_pending = false;
         for (int i = set; i < n_local; i += 2) {
             const int2 * tp = reinterpret_cast<const int2 *>(a.tiles + tile);      // 24-byte records, 8-byte aligned
@@ -267,111 +303,116 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attention_band_tc_kernel(const 
             if (head >= a.heads) { head -= a.heads; ++tile; }
             const int r0 = t01.x, tn = t01.y, pos0 = t23.y, utt_len = t45.y;
             const int k = i >> 1;
-            // this thread's row: query r = 32 quad + lane of the tile, position pos0 + r; it sees score columns
-            // [32 quad, 32 quad + 96) as idx 0..95; its own key is idx lane + 32; the band is idx in [lo, hi]
+            // this thread's row: query r = 32 quad + lane of the tile, position pos0 + r; the quadrant sees score columns
+            // [32 quad, 32 quad + 96) as idx 0..95; the row's own key is idx lane + 32; its band is idx in [lo, hi]
             const int r = quad * 32 + lane;
             const int pos = pos0 + r;
             int lo = lane + 32 - min(hw, pos), hi = lane + 32 + min(hw, utt_len - 1 - pos);
             if (r >= tn || hi < lo) { lo = 1 << 20; hi = lo; }
             const unsigned span = (unsigned) (hi - lo);
+            const int d0 = 48 * half - lo;                          // idx of this half's element e is 48 half + e
 
             const uint32_t s_tmem = tmem + set * 256 + lane_addr;
             bar_wait(s_full(set), k & 1);
             fence_after();
             float m = -INFINITY, l = 0.0f;
-            uint32_t pw[48];
+            uint32_t pw[24];
             {
-                uint32_t raw[3][32];
+                uint32_t raw[3][16];
 #pragma unroll
-                for (int c = 0; c < 3; ++c) tmem_ld32(s_tmem + quad * 32 + c * 32, raw[c]);
+                for (int c = 0; c < 3; ++c) tmem_ld16(s_tmem + quad * 32 + half * 48 + c * 16, raw[c]);
                 tmem_ld_wait();
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
 #pragma unroll
-                    for (int e = 0; e < 32; ++e) {
-                        const float v = (unsigned) (c * 32 + e - lo) <= span ? __uint_as_float(raw[c][e]) : -INFINITY;
+                    for (int e = 0; e < 16; ++e) {
+                        const float v = (unsigned) (c * 16 + e + d0) <= span ? __uint_as_float(raw[c][e]) : -INFINITY;
                         raw[c][e] = __float_as_uint(v);
                         m = fmaxf(m, v);
                     }
                 }
+                tmem_st1(s_tmem + AT_K + half, __float_as_uint(m));
+                tmem_st_wait();
+                pair_sync();
+                m = fmaxf(m, __uint_as_float(tmem_ld1(s_tmem + AT_K + (half ^ 1))));
                 if (m == -INFINITY) m = 0.0f;
                 const float ml2 = -m * 1.4426950408889634f;       // exp(s - m) = 2^(s log2e - m log2e): one FFMA + MUFU.EX2
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
 #pragma unroll
-                    for (int e = 0; e < 32; e += 2) {
+                    for (int e = 0; e < 16; e += 2) {
                         const float p0 = ex2_fast(fmaf(__uint_as_float(raw[c][e]), 1.4426950408889634f, ml2));
                         const float p1 = ex2_fast(fmaf(__uint_as_float(raw[c][e + 1]), 1.4426950408889634f, ml2));
                         l += p0 + p1;
-                        pw[(c * 32 + e) >> 1] = pk<BF16>(p0, p1);
+                        pw[(c * 16 + e) >> 1] = pk<BF16>(p0, p1);
                     }
                 }
+                tmem_st1(s_tmem + AT_K + 2 + half, __float_as_uint(l));
             }
-            // P over the S columns of this row: word w holds keys 2w, 2w+1; the quadrant's 48 words sit at column 16 quad,
-            // the other three 16-word blocks of the 96 are zero
+            // P over the S columns of this row: word w holds keys 2w, 2w+1; the quadrant's 48 words sit at column 16 quad
+            // (this half's 24 at + 24 half); the other 48 of the row's 96 words are zero, 24 written by each half
             {
-                uint32_t zero16[16];
+                uint32_t zero8[8];
 #pragma unroll
-                for (int e = 0; e < 16; ++e) zero16[e] = 0u;
-                const uint32_t (*pw16)[16] = reinterpret_cast<const uint32_t (*)[16]>(pw);
-                tmem_st16(s_tmem + quad * 16, pw16[0]);
-                tmem_st16(s_tmem + quad * 16 + 16, pw16[1]);
-                tmem_st16(s_tmem + quad * 16 + 32, pw16[2]);
-                // the three blocks outside [quad, quad + 3): columns (quad + 3 + j) mod 6 blocks
+                for (int e = 0; e < 8; ++e) zero8[e] = 0u;
+                const uint32_t (*pw8)[8] = reinterpret_cast<const uint32_t (*)[8]>(pw);
+#pragma unroll
+                for (int j = 0; j < 3; ++j) tmem_st8(s_tmem + quad * 16 + half * 24 + j * 8, pw8[j]);
 #pragma unroll
                 for (int j = 0; j < 3; ++j) {
-                    int blk = quad + 3 + j;
-                    if (blk >= 6) blk -= 6;
-                    tmem_st16(s_tmem + blk * 16, zero16);
+                    int w0 = quad * 16 + 48 + half * 24 + j * 8;   // words [16 quad + 48, 16 quad + 96) mod 96
+                    if (w0 >= 96) w0 -= 96;
+                    tmem_st8(s_tmem + w0, zero8);
                 }
             }
             tmem_st_wait();
+            if (store_pending) {      // half 0's lane 0 issued the previous store of this box; the pair barrier below orders it
+                if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                store_pending = false;
+            }
+            pair_sync();              // partner's row sum is in TMEM; the previous store has read the box
+            l += __uint_as_float(tmem_ld1(s_tmem + AT_K + 2 + (half ^ 1)));   // read BEFORE p_full: PV overwrites these columns
+            const float inv = l > 0.0f ? __fdividef(1.0f, l) : 0.0f;
             fence_before();
             __syncwarp();
             if (lane == 0) bar_arrive(p_full(set));
 
-            // ---- O row = (P V) / l -> swizzled output box -> TMA store ----
-            const float inv = l > 0.0f ? __fdividef(1.0f, l) : 0.0f;
-            if (store_pending) {
-                if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-                __syncwarp();
-                store_pending = false;
-            }
+            // ---- O row = (P V) / l -> the pair's swizzled output box -> one TMA store ----
             bar_wait(o_full(set), k & 1);
             fence_after();
             {
-                uint32_t o[2][32];
-                tmem_ld32(s_tmem + AT_K, o[0]);
-                tmem_ld32(s_tmem + AT_K + 32, o[1]);
+                uint32_t o[32];
+                tmem_ld32(s_tmem + AT_K + half * 32, o);
                 tmem_ld_wait();
                 const uint32_t row = obuf + lane * 128;
 #pragma unroll
-                for (int c = 0; c < 8; ++c) {                   // 16-byte chunk c = head-dim columns [8c, 8c+8)
-                    const uint32_t * s8 = &o[c >> 2][(c & 3) * 8];
+                for (int c = 0; c < 4; ++c) {                   // 16-byte chunk 4 half + c = head-dim columns [32 half + 8c, +8)
+                    const uint32_t * s8 = &o[c * 8];
                     const uint32_t w0 = pk<BF16>(__uint_as_float(s8[0]) * inv, __uint_as_float(s8[1]) * inv);
                     const uint32_t w1 = pk<BF16>(__uint_as_float(s8[2]) * inv, __uint_as_float(s8[3]) * inv);
                     const uint32_t w2 = pk<BF16>(__uint_as_float(s8[4]) * inv, __uint_as_float(s8[5]) * inv);
                     const uint32_t w3 = pk<BF16>(__uint_as_float(s8[6]) * inv, __uint_as_float(s8[7]) * inv);
-                    asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(row + (((uint32_t) (c ^ lane) & 7u) << 4)),
+                    asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(row + (((uint32_t) ((4 * half + c) ^ lane) & 7u) << 4)),
                                  "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
                 }
             }
             fence_before();      // the TMEM reads above are ordered before the next MMA that overwrites this set's columns
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            pair_sync();         // both halves of every row are in the box
             if (quad * 32 + 32 <= tn) {
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                __syncwarp();
-                if (lane == 0) {
-                    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
-                                 ::"l"((uint64_t) &a.map_out), "r"(obuf), "r"(cur_head * AT_HD), "r"(r0 + quad * 32) : "memory");
-                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                if (half == 0) {
+                    if (lane == 0) {
+                        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                                     ::"l"((uint64_t) &a.map_out), "r"(obuf), "r"(cur_head * AT_HD), "r"(r0 + quad * 32) : "memory");
+                        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                    }
+                    store_pending = true;
                 }
-                store_pending = true;
             } else if (quad * 32 < tn) {
-                // the utterance ends inside this warp's 32 rows: plain 16-byte stores of the rows that exist
-                __syncwarp();
+                // the utterance ends inside these 32 rows: plain 16-byte stores of the rows that exist (4 of 8 passes per half)
 #pragma unroll
-                for (int it = 0; it < 8; ++it) {
-                    const int c = lane + 32 * it, rr = c >> 3, ch = c & 7;
+                for (int it = 0; it < 4; ++it) {
+                    const int c = lane + 32 * (it + 4 * half), rr = c >> 3, ch = c & 7;
                     if (quad * 32 + rr < tn) {
                         uint4 v;
                         asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
@@ -379,7 +420,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attention_band_tc_kernel(const 
                         *reinterpret_cast<uint4 *>(a.out + (size_t) (r0 + quad * 32 + rr) * a.dim + cur_head * AT_HD + ch * 8) = v;
                     }
                 }
-                __syncwarp();
+                pair_sync();     // the box may be rewritten only after both halves have read it
             }
         }
         if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
