@@ -45,7 +45,7 @@ struct attc_args {
     CUtensorMap map_q;       // [rows, 3*dim] 16-bit, box 64 cols x 128 rows, SWIZZLE_128B
     CUtensorMap map_kv;      // same tensor, box 64 cols x 192 rows
     CUtensorMap map_out;     // [rows, dim] 16-bit, box 64 cols x 32 rows, SWIZZLE_128B
-    int rows, dim, heads, half_window, n_items, dtype;
+    int rows, dim, heads, half_window, n_items, dtype, n_tiles, reverse;
     const row_tile * tiles;  // <= 128-row runs inside one utterance
     uint16_t * out;
 };
@@ -205,7 +205,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attention_band_tc_kernel(const 
         for (int i0 = 0; i0 < n_local; i0 += 32) {
             int my_tile = tile + lane * step_t, my_head = head + lane * step_h;
             my_tile += my_head / a.heads; my_head %= a.heads;
-            const int my_r0 = i0 + lane < n_local ? __ldg(&a.tiles[my_tile].row0) : 0;
+            const int my_r0 = i0 + lane < n_local ? __ldg(&a.tiles[a.reverse ? a.n_tiles - 1 - my_tile : my_tile].row0) : 0;
             const int n_here = min(32, n_local - i0);
             for (int l = 0; l < n_here; ++l) {
                 const int r0 = __shfl_sync(0xffffffffu, my_r0, l);
@@ -296,7 +296,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attention_band_tc_kernel(const 
         };
         bool store_pending = false;
         for (int i = set; i < n_local; i += 2) {
-            const int2 * tp = reinterpret_cast<const int2 *>(a.tiles + tile);      // 24-byte records, 8-byte aligned
+            const int2 * tp = reinterpret_cast<const int2 *>(a.tiles + (a.reverse ? a.n_tiles - 1 - tile : tile));   // 24-byte records
             const int2 t01 = __ldg(tp), t23 = __ldg(tp + 1), t45 = __ldg(tp + 2);  // (row0, n) (utt, pos0) (utt_row0, utt_len)
             const int cur_head = head;
             tile += gstep_t; head += gstep_h;
@@ -458,7 +458,7 @@ void launch_attention_tc(const CUtensorMap & map_q, const CUtensorMap & map_kv, 
     attc_args a;
     a.map_q = map_q; a.map_kv = map_kv; a.map_out = map_out;
     a.rows = rows; a.dim = dim; a.heads = heads; a.half_window = window / 2; a.dtype = dtype;
-    a.n_items = n_tiles * heads;
+    a.n_items = n_tiles * heads; a.n_tiles = n_tiles; a.reverse = traversal_reverse();
     a.tiles = tiles128; a.out = (uint16_t *) out16;
     static bool configured[64] = {false};
     int dev = 0;

@@ -49,6 +49,18 @@ inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t s
 }
 #endif
 
+// ---------------------------------------------------------------------------------------------
+// Ping-pong traversal.  Every kernel of the decode chain streams [rows, channels] activations that its predecessor has
+// just written, and the working set of one stage (100-260 MB) is larger than the 126 MB L2: if both walk the rows in
+// the same direction the consumer starts with the rows that left the L2 longest ago and misses all the way.  The
+// engine therefore flips the direction from launch to launch: a kernel launched "reversed" maps its block / tile index
+// b to (count - 1 - b), so it begins with the rows the previous kernel wrote LAST.  Results do not depend on the order
+// (no kernel mixes rows).  traversal_reverse() is the flag the launchers read; MIO_TTS_B200_PINGPONG=0 pins it to 0.
+// ---------------------------------------------------------------------------------------------
+int traversal_reverse();
+void set_traversal_reverse(int rev);
+#define MIO_BLOCK_X(rev) ((rev) ? gridDim.x - 1 - blockIdx.x : blockIdx.x)
+
 // 16-bit operand formats of the tensor-core GEMMs (tcgen05 kind::f16 a/b_format field)
 enum op16 : int { OP_F16 = 0, OP_BF16 = 1 };
 
@@ -104,6 +116,7 @@ struct gemm_args {
     // from the epilogue (double atomics on gn_stats[(utt * gn_groups + g) * 2 + {0,1}], gap rows excluded) instead of
     // a separate pass over the output.  Needs row_utt, N % 32 == 0 and N / gn_groups == 16 or a multiple of 32.
     double * gn_stats; int gn_groups;
+    int reverse_m;                       // walk the row tiles from the last to the first (ping-pong traversal): set by gemm_launch
 };
 inline bool gemm_gn_stats_ok(int N, int groups) {
     if (groups <= 0 || N % groups != 0 || N % 32 != 0) return false;

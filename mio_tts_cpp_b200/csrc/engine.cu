@@ -408,6 +408,9 @@ void engine::reserve(int n_codes, int batch) {
 // -------------------------------------------------------------------------------------------------
 // kernels in sequence
 // -------------------------------------------------------------------------------------------------
+// every kernel of the chain walks the rows in the opposite direction of its predecessor (ping-pong traversal, common.h)
+void engine::flip() { set_traversal_reverse(dir_ ^= 1); }
+
 void engine::gemm(const dbuf & a, const dev_linear & w, int M, int epilogue, void * out, int ldo, int out_dtype,
                   const float * bias, const float * res, int ldr, const float * gate, const seq_layout * lay,
                   const float2 * rope, int heads, double * gn_stats, int gn_groups) {
@@ -434,6 +437,7 @@ void engine::gemm(const dbuf & a, const dev_linear & w, int M, int epilogue, voi
         while (gemm_ev_.size() < evi + 2) { cudaEvent_t e; MIO_CUDA(cudaEventCreate(&e)); gemm_ev_.push_back(e); }
         MIO_CUDA(cudaEventRecord(gemm_ev_[evi], st_));
     }
+    flip();
     gemm_launch(g, mdl->num_sms, st_);
     if (prof_gemm_) {
         MIO_CUDA(cudaEventRecord(gemm_ev_[evi + 1], st_));
@@ -453,11 +457,11 @@ void engine::run_tblock(float * x, const seq_layout & L, const tblock & blk, int
     const int ldt = mdl->linear_dtype;
     const float * cv = (const float *) cond_.p;
     if (cond)
-        launch_layernorm(x, rows, dim, hp.norm_eps, nullptr, nullptr, cv, mdl->cond_total, blk.cond_attn_off,
-                         blk.cond_attn_off + dim, L.d_row_utt, act16_.p, ldt, nullptr, st_);
+        { flip(); launch_layernorm(x, rows, dim, hp.norm_eps, nullptr, nullptr, cv, mdl->cond_total, blk.cond_attn_off,
+                         blk.cond_attn_off + dim, L.d_row_utt, act16_.p, ldt, nullptr, st_); }
     else
-        launch_layernorm(x, rows, dim, hp.norm_eps, blk.ln1.w, blk.ln1.b, nullptr, 0, 0, 0, L.d_row_utt, act16_.p, ldt,
-                         nullptr, st_);
+        { flip(); launch_layernorm(x, rows, dim, hp.norm_eps, blk.ln1.w, blk.ln1.b, nullptr, 0, 0, 0, L.d_row_utt, act16_.p, ldt,
+                         nullptr, st_); }
     gemm(act16_, blk.qkv, rows, EPI_ROPE16, qkv16_.p, 3 * dim, ldt, nullptr, nullptr, 0, nullptr, &L, rope, heads);
     size_t evi = 0;
     if (prof_gemm_) {
@@ -466,21 +470,21 @@ void engine::run_tblock(float * x, const seq_layout & L, const tblock & blk, int
         MIO_CUDA(cudaEventRecord(gemm_ev_[evi], st_));
     }
     if (!force_generic_attention && attention_tc_ok(dim, heads, window))
-        launch_attention_tc(xmap(qkv16_.p, rows, 3 * dim, 128), xmap(qkv16_.p, rows, 3 * dim, 192), xmap(att16_.p, rows, dim, 32),
-                            att16_.p, ldt, dim, heads, window, rows, L.d_tiles128, L.n_tiles128, mdl->num_sms, st_);
+        { flip(); launch_attention_tc(xmap(qkv16_.p, rows, 3 * dim, 128), xmap(qkv16_.p, rows, 3 * dim, 192), xmap(att16_.p, rows, dim, 32),
+                            att16_.p, ldt, dim, heads, window, rows, L.d_tiles128, L.n_tiles128, mdl->num_sms, st_); }
     else if (!force_generic_attention && attention_tma_ok(dim, heads, window))
-        launch_attention_tma(xmap(qkv16_.p, rows, 3 * dim, 64), xmap(att16_.p, rows, dim, 16), att16_.p, ldt, dim, heads, window,
-                             rows, L.d_tiles, L.n_tiles, mdl->num_sms, st_);
+        { flip(); launch_attention_tma(xmap(qkv16_.p, rows, 3 * dim, 64), xmap(att16_.p, rows, dim, 16), att16_.p, ldt, dim, heads, window,
+                             rows, L.d_tiles, L.n_tiles, mdl->num_sms, st_); }
     else
-        launch_attention(qkv16_.p, att16_.p, ldt, dim, heads, window, L.d_tiles, L.n_tiles, force_generic_attention, st_);
+        { flip(); launch_attention(qkv16_.p, att16_.p, ldt, dim, heads, window, L.d_tiles, L.n_tiles, force_generic_attention, st_); }
     if (prof_gemm_) { MIO_CUDA(cudaEventRecord(gemm_ev_[evi + 1], st_)); attn_ev_.push_back(evi); }
     gemm(att16_, blk.o, rows, EPI_STORE32, x, dim, 0, nullptr, x, dim, cond ? cv + blk.cond_attn_off + 2 * dim : nullptr, &L);
     if (cond)
-        launch_layernorm(x, rows, dim, hp.norm_eps, nullptr, nullptr, cv, mdl->cond_total, blk.cond_ffn_off,
-                         blk.cond_ffn_off + dim, L.d_row_utt, act16_.p, ldt, nullptr, st_);
+        { flip(); launch_layernorm(x, rows, dim, hp.norm_eps, nullptr, nullptr, cv, mdl->cond_total, blk.cond_ffn_off,
+                         blk.cond_ffn_off + dim, L.d_row_utt, act16_.p, ldt, nullptr, st_); }
     else
-        launch_layernorm(x, rows, dim, hp.norm_eps, blk.ln2.w, blk.ln2.b, nullptr, 0, 0, 0, L.d_row_utt, act16_.p, ldt,
-                         nullptr, st_);
+        { flip(); launch_layernorm(x, rows, dim, hp.norm_eps, blk.ln2.w, blk.ln2.b, nullptr, 0, 0, 0, L.d_row_utt, act16_.p, ldt,
+                         nullptr, st_); }
     gemm(act16_, blk.gate_up, rows, EPI_SWIGLU16, ff16_.p, ff, ldt, nullptr, nullptr, 0, nullptr, &L);
     gemm(ff16_, blk.down, rows, EPI_STORE32, x, dim, 0, nullptr, x, dim, cond ? cv + blk.cond_ffn_off + 2 * dim : nullptr, &L);
 }
@@ -490,9 +494,9 @@ void engine::run_tblock(float * x, const seq_layout & L, const tblock & blk, int
 void engine::group_norm_silu(const float * x, const seq_layout & L, int channels, int groups, const dev_norm & n,
                              int slot, bool stats_ready) {
     double * stats = gn_slot_ptr(slot);
-    if (!stats_ready) launch_gn_stats(x, channels, groups, L.d_tiles, L.n_tiles, stats, st_);
-    launch_gn_apply(x, L.rows, channels, groups, stats, L.d_len, mdl->hp.group_norm_eps, n.w, n.b, L.d_row_utt, act16_.p,
-                    mdl->conv_dtype, st_);
+    if (!stats_ready) { flip(); launch_gn_stats(x, channels, groups, L.d_tiles, L.n_tiles, stats, st_); }
+    { flip(); launch_gn_apply(x, L.rows, channels, groups, stats, L.d_len, mdl->hp.group_norm_eps, n.w, n.b, L.d_row_utt, act16_.p,
+                    mdl->conv_dtype, st_); }
 }
 
 // resnet_block_eval, /root/reference/src/miocodec-decoder.cpp:1293-1330 (x updated in place, y is scratch).
@@ -614,6 +618,7 @@ void engine::run_direct(bool with_istft, stage_times * prof, int stop_stage) {
     launch_gather(mdl->tok_embd, d_codes_, xt, tok_.rows, pd, st_);
     for (const tblock & b : mdl->prenet)
         run_tblock(xt, tok_, b, pd, hp.prenet_heads, hp.prenet_ff, hp.prenet_window, rope_p_, false);
+    flip();
     launch_layernorm(xt, tok_.rows, pd, hp.norm_eps, mdl->prenet_norm.w, mdl->prenet_norm.b, nullptr, 0, 0, 0,
                      tok_.d_row_utt, act16_.p, ldt, nullptr, st_);
     gemm(act16_, mdl->prenet_out, tok_.rows, EPI_STORE16, ff16_.p, dd, ldt, mdl->prenet_out.bias, nullptr, 0, nullptr, &tok_);
@@ -623,6 +628,7 @@ void engine::run_direct(bool with_istft, stage_times * prof, int stop_stage) {
     // ---- x2 transposed conv as one GEMM + interpolate to the decoder frame count (:1368-1374) ----
     float * fx = (float *) fx_.p, * fy = (float *) fy_.p, * ft = (float *) ft_.p;
     gemm(ff16_, mdl->upsample, tok_.rows, EPI_STORE32, ft, 2 * dd, 0, mdl->upsample.bias, nullptr, 0, nullptr, &tok_);
+    flip();
     launch_interp(ft, d_tok2_row0_, d_tok2_len_, fx, frm_.rows, dd, frm_.d_row_utt, frm_.d_row_pos, frm_.d_len, st_);
     if (stop(2, fx, dd, 0, 0, &frm_)) return;
     int gn_slot = 0;
@@ -636,11 +642,11 @@ void engine::run_direct(bool with_istft, stage_times * prof, int stop_stage) {
     for (const tblock & b : mdl->decoder)
         run_tblock(fx, frm_, b, dd, hp.decoder_heads, hp.decoder_ff, hp.decoder_window, rope_d_, hp.dynamic_global);
     if (hp.dynamic_global)
-        launch_layernorm(fx, frm_.rows, dd, hp.norm_eps, nullptr, nullptr, (const float *) cond_.p, mdl->cond_total,
-                         mdl->cond_final_off, mdl->cond_final_off + dd, frm_.d_row_utt, nullptr, 0, fy, st_);
+        { flip(); launch_layernorm(fx, frm_.rows, dd, hp.norm_eps, nullptr, nullptr, (const float *) cond_.p, mdl->cond_total,
+                         mdl->cond_final_off, mdl->cond_final_off + dd, frm_.d_row_utt, nullptr, 0, fy, st_); }
     else
-        launch_layernorm(fx, frm_.rows, dd, hp.norm_eps, mdl->decoder_norm.w, mdl->decoder_norm.b, nullptr, 0, 0, 0,
-                         frm_.d_row_utt, nullptr, 0, fy, st_);
+        { flip(); launch_layernorm(fx, frm_.rows, dd, hp.norm_eps, mdl->decoder_norm.w, mdl->decoder_norm.b, nullptr, 0, 0, 0,
+                         frm_.d_row_utt, nullptr, 0, fy, st_); }
     std::swap(fx, fy);
     mark(3);
     if (stop(4, fx, dd, 0, 0, &frm_)) return;
@@ -655,6 +661,7 @@ void engine::run_direct(bool with_istft, stage_times * prof, int stop_stage) {
     for (size_t i = 0; i < mdl->ups.size(); ++i) {
         const upstage & s = mdl->ups[i];
         const seq_layout & nxt = ups_[i];
+        flip();
         launch_cast16(fx, act16_.p, mdl->conv_dtype, (size_t) cur->rows * cur_c, st_);
         gemm(act16_, s.up, cur->rows, EPI_STORE32, ft, s.ksize * s.cout, 0, nullptr, nullptr, 0, nullptr, cur);
         launch_convt_fold_snake(ft, s.ksize * s.cout, cur->d_row0, cur->d_len, fy, nxt.rows, s.cout, s.ksize, s.factor,
@@ -665,12 +672,15 @@ void engine::run_direct(bool with_istft, stage_times * prof, int stop_stage) {
         cur_c = s.cout;
     }
     if (!mdl->ups.empty()) {
+        flip();
         launch_cast16(fx, act16_.p, ldt, (size_t) cur->rows * cur_c, st_);
         gemm(act16_, mdl->up_out_proj, cur->rows, EPI_STORE32, ft, mdl->head_in, 0, mdl->up_out_proj.bias, nullptr, 0,
              nullptr, cur);
         launch_snake(ft, cur->rows, mdl->head_in, mdl->out_snake_a, mdl->out_snake_inv_b, st_);
+        flip();
         launch_cast16(ft, act16_.p, ldt, (size_t) cur->rows * mdl->head_in, st_);
     } else {
+        flip();
         launch_cast16(fx, act16_.p, ldt, (size_t) cur->rows * cur_c, st_);
     }
     gemm(act16_, mdl->head, cur->rows, EPI_STORE32, spec_buf_.p, spec_pitch_, 0, mdl->head.bias, nullptr, 0, nullptr, cur);

@@ -143,6 +143,8 @@ private:
                       bool feeds_next);
     void group_norm_silu(const float * x, const seq_layout & L, int channels, int groups, const dev_norm & n, int slot,
                          bool stats_ready);
+    void flip();
+    int dir_ = 0;
     double * gn_slot_ptr(int slot) { return (double *) gn_stats_.p + (size_t) slot * n_utt_ * gn_groups_max_ * 2; }
 };
 

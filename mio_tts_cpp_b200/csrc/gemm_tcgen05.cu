@@ -413,7 +413,10 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
         const int t = item_tile(w);
         return (t % num_n_tiles) * BN + (w < split_from ? 0 : ((w - split_from) & ((1 << split_shift) - 1)) * (BN >> split_shift));
     };
-    auto item_m0 = [&](int w) { return (item_tile(w) / num_n_tiles) * TILE_M; };
+    auto item_m0 = [&](int w) {     // reverse_m: row tiles from the last to the first (ping-pong traversal, common.h)
+        const int mt = item_tile(w) / num_n_tiles;
+        return (a.reverse_m ? num_m_tiles - 1 - mt : mt) * TILE_M;
+    };
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < C::STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
@@ -817,6 +820,13 @@ template <int BN, int EW, int NCTA> void launch_bn(const gemm_args & a, int num_
 
 } // namespace
 
+namespace { thread_local int t_traversal_reverse = 0; }
+int traversal_reverse() { return t_traversal_reverse; }
+void set_traversal_reverse(int rev) {
+    static const bool on = [] { const char * e = std::getenv("MIO_TTS_B200_PINGPONG"); return !(e && e[0] == '0'); }();
+    t_traversal_reverse = on ? (rev ? 1 : 0) : 0;
+}
+
 bool pdl_enabled() {
     static int v = -1;
     if (v < 0) { const char * e = std::getenv("MIO_TTS_B200_PDL"); v = (e && e[0] == '0') ? 0 : 1; }
@@ -871,6 +881,7 @@ void gemm_launch(const gemm_args & a, int num_sms, cudaStream_t st) {
         ncta = (c && std::atoi(c) == 1) ? 1 : 2;
     }
     gemm_args g = a;
+    g.reverse_m = traversal_reverse();
     if (g.gn_stats != nullptr && (a.epilogue != EPI_STORE32 || a.row_utt == nullptr || a.bias == nullptr || a.gate != nullptr ||
                                   !gemm_gn_stats_ok(a.N, a.gn_groups)))
         throw cuda_error("gemm: GroupNorm statistics need the fp32-store epilogue with bias, row_utt, no gate, and a supported group width");

@@ -131,12 +131,12 @@ template <int NV, int RW>
 __global__ void __launch_bounds__(256) layernorm_kernel(const float * __restrict__ x, int rows, float eps, const float * __restrict__ w,
                                                         const float * __restrict__ b, const float * __restrict__ cond, int cond_ld,
                                                         int shift_off, int scale_off, const int * __restrict__ row_utt, void * out16,
-                                                        int out_dtype, float * out32) {
+                                                        int out_dtype, float * out32, int rev) {
     MIO_PDL_PROLOGUE();
     constexpr int DIM = NV * 128;
     // RW rows per warp, all their loads in flight together; the affine / AdaLN parameters of the first row's utterance
     // are fetched before the reductions (the other rows almost always share them) so nothing waits on them afterwards
-    const int row0 = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * RW;
+    const int row0 = (MIO_BLOCK_X(rev) * (blockDim.x >> 5) + (threadIdx.x >> 5)) * RW;
     if (row0 >= rows) return;
     const int lane = threadIdx.x & 31;
     float4 v[RW][NV];
@@ -222,9 +222,9 @@ __global__ void layernorm_generic_kernel(const float * __restrict__ x, int rows,
                                          const float * __restrict__ w, const float * __restrict__ b,
                                          const float * __restrict__ cond, int cond_ld, int shift_off, int scale_off,
                                          const int * __restrict__ row_utt, void * out16, int out_dtype,
-                                         float * out32) {
+                                         float * out32, int rev) {
     MIO_PDL_PROLOGUE();
-    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int row = MIO_BLOCK_X(rev) * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= rows) return;
     const int lane = threadIdx.x & 31;
     const int utt = row_utt ? row_utt[row] : 0;
@@ -247,9 +247,9 @@ __global__ void layernorm_generic_kernel(const float * __restrict__ x, int rows,
     }
 }
 
-__global__ void cast16_kernel(const float * __restrict__ x, void * out16, int out_dtype, size_t n4) {
+__global__ void cast16_kernel(const float * __restrict__ x, void * out16, int out_dtype, size_t n4, int rev) {
     MIO_PDL_PROLOGUE();
-    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t i = (size_t) MIO_BLOCK_X(rev) * blockDim.x + threadIdx.x;
     if (i >= n4) return;
     const float4 v = reinterpret_cast<const float4 *>(x)[i];
     uint2 o;
@@ -262,10 +262,10 @@ __global__ void cast16_kernel(const float * __restrict__ x, void * out16, int ou
 //      (ggml_group_norm, ggml-cpu/ops.cpp:3955-4028: double accumulators).  One block per <=64-row tile. ----
 template <int VEC>
 __global__ void gn_stats_kernel(const float * __restrict__ x, int dim, int groups, const row_tile * __restrict__ tiles,
-                                double * __restrict__ stats) {
+                                double * __restrict__ stats, int rev) {
     MIO_PDL_PROLOGUE();
     extern __shared__ double s_acc[];   // [groups][2]
-    const row_tile t = tiles[blockIdx.x];
+    const row_tile t = tiles[MIO_BLOCK_X(rev)];
     for (int i = threadIdx.x; i < groups * 2; i += blockDim.x) s_acc[i] = 0.0;
     __syncthreads();
     const int cpg = dim / groups;
@@ -312,10 +312,10 @@ __global__ void gn_apply_kernel(const float * __restrict__ x, int rows, int dim,
                                 const double * __restrict__ stats, const int * __restrict__ utt_len, float eps,
                                 const float * __restrict__ w,
                                 const float * __restrict__ b, const int * __restrict__ row_utt, void * out16,
-                                int out_dtype) {
+                                int out_dtype, int rev) {
     MIO_PDL_PROLOGUE();
     const int c4n = dim >> 2;
-    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t i = (size_t) MIO_BLOCK_X(rev) * blockDim.x + threadIdx.x;
     if (i >= (size_t) rows * c4n) return;
     const int row = (int) (i / c4n);
     const int c4 = (int) (i % c4n);
@@ -348,7 +348,7 @@ __global__ void gn_apply_fast_kernel(const float * __restrict__ x, int rows, int
                                      const double * __restrict__ stats, const int * __restrict__ utt_len, float eps,
                                      const float * __restrict__ w,
                                      const float * __restrict__ b, const int * __restrict__ row_utt, void * out16,
-                                     int out_dtype) {
+                                     int out_dtype, int rev) {
     MIO_PDL_PROLOGUE();
     const int c4n = dim >> 2;
     const int rpb = blockDim.x / c4n;                 // rows per block pass
@@ -356,7 +356,7 @@ __global__ void gn_apply_fast_kernel(const float * __restrict__ x, int rows, int
     const int g = (c4 * 4) / (dim / groups);
     const float4 ww = __ldg(reinterpret_cast<const float4 *>(w) + c4);
     const float4 bb = __ldg(reinterpret_cast<const float4 *>(b) + c4);
-    const int row_base = blockIdx.x * rpb * ROWS_PER_THREAD + threadIdx.x / c4n;
+    const int row_base = MIO_BLOCK_X(rev) * rpb * ROWS_PER_THREAD + threadIdx.x / c4n;
     float4 v[ROWS_PER_THREAD];
     int utt[ROWS_PER_THREAD];
 #pragma unroll
@@ -524,10 +524,10 @@ void launch_layernorm(const float * x, int rows, int dim, float eps, const float
     case NV:                                                                                                     \
         if (NV <= 4)                                                                                             \
             launch_pdl(layernorm_kernel<NV, 2>, dim3(grid2), dim3(256), 0, st, x, rows, eps, w, b, cond, cond_ld, shift_off,         \
-                       scale_off, row_utt, out16, out_dtype, out32);                                            \
+                       scale_off, row_utt, out16, out_dtype, out32, traversal_reverse());                                            \
         else                                                                                                     \
             launch_pdl(layernorm_kernel<NV, 1>, dim3(grid), dim3(256), 0, st, x, rows, eps, w, b, cond, cond_ld, shift_off,          \
-                       scale_off, row_utt, out16, out_dtype, out32);                                            \
+                       scale_off, row_utt, out16, out_dtype, out32, traversal_reverse());                                            \
         break;
     if ((dim % 128) == 0 && dim <= 1024 && (!cond || ((cond_ld | shift_off | scale_off) & 3) == 0)) {
         switch (dim / 128) {
@@ -535,7 +535,7 @@ void launch_layernorm(const float * x, int rows, int dim, float eps, const float
         }
     } else {
         launch_pdl(layernorm_generic_kernel, dim3(grid), dim3(256), 0, st, x, rows, dim, eps, w, b, cond, cond_ld, shift_off, scale_off,
-                                                       row_utt, out16, out_dtype, out32);
+                                                       row_utt, out16, out_dtype, out32, traversal_reverse());
     }
 #undef LN_CASE
     MIO_CUDA(cudaGetLastError());
@@ -545,7 +545,7 @@ void launch_layernorm(const float * x, int rows, int dim, float eps, const float
 void launch_cast16(const float * x, void * out16, int out_dtype, size_t n, cudaStream_t st) {
     if (n == 0) return;
     if (n & 3) throw cuda_error("cast16: element count must be a multiple of 4");
-    launch_pdl(cast16_kernel, dim3(blocks_for(n >> 2, 256)), dim3(256), 0, st, x, out16, out_dtype, n >> 2);
+    launch_pdl(cast16_kernel, dim3(blocks_for(n >> 2, 256)), dim3(256), 0, st, x, out16, out_dtype, n >> 2, traversal_reverse());
     MIO_CUDA(cudaGetLastError());
     count_launch();
 }
@@ -558,10 +558,10 @@ void launch_gn_stats(const float * x, int dim, int groups, const row_tile * tile
     if ((cpg & 3) == 0) {
         const int cols = dim / 4;
         const int threads = cols >= 256 ? ((cols + 31) / 32) * 32 : 256;
-        launch_pdl(gn_stats_kernel<4>, dim3(n_tiles), dim3(threads > 1024 ? 1024 : threads), smem, st, x, dim, groups, tiles, stats);
+        launch_pdl(gn_stats_kernel<4>, dim3(n_tiles), dim3(threads > 1024 ? 1024 : threads), smem, st, x, dim, groups, tiles, stats, traversal_reverse());
     } else {
         const int threads = dim >= 256 ? ((dim + 31) / 32) * 32 : 256;
-        launch_pdl(gn_stats_kernel<1>, dim3(n_tiles), dim3(threads > 1024 ? 1024 : threads), smem, st, x, dim, groups, tiles, stats);
+        launch_pdl(gn_stats_kernel<1>, dim3(n_tiles), dim3(threads > 1024 ? 1024 : threads), smem, st, x, dim, groups, tiles, stats, traversal_reverse());
     }
     MIO_CUDA(cudaGetLastError());
     count_launch();
@@ -576,10 +576,10 @@ void launch_gn_apply(const float * x, int rows, int dim, int groups, const doubl
         constexpr int RPT = 4;
         const int rows_per_block = (256 / c4n) * RPT;
         launch_pdl(gn_apply_fast_kernel<RPT>, dim3(blocks_for((size_t) rows, rows_per_block)), dim3(256), 0, st, 
-            x, rows, dim, groups, stats, utt_len, eps, w, b, row_utt, out16, out_dtype);
+            x, rows, dim, groups, stats, utt_len, eps, w, b, row_utt, out16, out_dtype, traversal_reverse());
     } else {
         launch_pdl(gn_apply_kernel, dim3(blocks_for((size_t) rows * (dim >> 2), 256)), dim3(256), 0, st, 
-            x, rows, dim, groups, stats, utt_len, eps, w, b, row_utt, out16, out_dtype);
+            x, rows, dim, groups, stats, utt_len, eps, w, b, row_utt, out16, out_dtype, traversal_reverse());
     }
     MIO_CUDA(cudaGetLastError());
     count_launch();
