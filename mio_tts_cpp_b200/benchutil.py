@@ -31,6 +31,20 @@ def config2_workload(rank=0, batch=64, n_codes=400):
             for i in range(batch)]
 
 
+def reduce_over_ranks(dist, device, step_ms, audio_s):
+    """Multi-GPU aggregation of a replica run (no data-path collective): the step time is the MAX over ranks, the work
+    is the SUM over ranks.  `dist` = torch.distributed (initialised) or None for a single process."""
+    if dist is None:
+        return float(step_ms), float(audio_s)
+    import torch
+
+    t = torch.tensor([step_ms], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    a = torch.tensor([audio_s], dtype=torch.float64, device=device)
+    dist.all_reduce(a, op=dist.ReduceOp.SUM)
+    return float(t.item()), float(a.item())
+
+
 def speaker_embedding():
     return np.load(os.path.join(ROOT, "tests", "golden", "en_female_emb.npy"))
 

@@ -12,14 +12,16 @@
 //   * the steady-state envelope (sum of hann^2 over the 4 overlapping frames) is tabulated once per CTA.
 #include "common.h"
 
+#include <cstdlib>
 #include <type_traits>
 #include <utility>
 
 namespace mio {
 namespace {
 
-constexpr int FW = 16;                 // warps (= frames in flight) per CTA
-constexpr int FTHREADS = FW * 32;
+// FW = warps (= frames in flight) per CTA, a template parameter: 16 with one CTA per SM, 8 with two, 4 with four.  A CTA's
+// warps move through the load / FFT phase and the overlap-add phase together, so CTAs that share an SM are what overlaps
+// one CTA's global loads with another's shared-memory work.
 
 struct fast_params {
     int n_freq, pad, frames_per_chunk;
@@ -235,9 +237,10 @@ __device__ __forceinline__ float2 polar_fast(float logmag, float phase) {
     return mul2(bc(mag), make_float2(c, s));
 }
 
-template <int N, int... RADIX>
-__global__ void __launch_bounds__(FTHREADS, 1) istft_fast_kernel(const fast_params P) {
+template <int FW, int N, int... RADIX>
+__global__ void __launch_bounds__(FW * 32, 16 / FW) istft_fast_kernel(const fast_params P) {
     MIO_PDL_PROLOGUE();
+    constexpr int FTHREADS = FW * 32;
     constexpr int M = N / 2, H = N / 4, CARRY = N - H, SPAN = FW * H, MP = padded_len<M>::value;
     constexpr int TWL = tw_table_len<M, 1, RADIX...>::value;
     static_assert(H % 4 == 0 && MP % 2 == 0 && TWL % 2 == 0, "16-byte rows");
@@ -394,8 +397,9 @@ __global__ void __launch_bounds__(FTHREADS, 1) istft_fast_kernel(const fast_para
     }
 }
 
-template <int N, int... RADIX>
+template <int FW, int N, int... RADIX>
 void launch_fast_t(fast_params P, const int * h_frames, int n_utt, int max_frames, cudaStream_t st) {
+    constexpr int FTHREADS = FW * 32;
     constexpr int M = N / 2, H = N / 4, MP = padded_len<M>::value;
     constexpr int TWL = tw_table_len<M, 1, RADIX...>::value;
     const size_t smem = (size_t) FW * MP * 8 + (size_t) TWL * 8 + (size_t) (M / 2 + 2) * 8 + (size_t) N * 4 + (size_t) H * 4 +
@@ -405,16 +409,16 @@ void launch_fast_t(fast_params P, const int * h_frames, int n_utt, int max_frame
     int dev = 0;
     MIO_CUDA(cudaGetDevice(&dev));
     if (!configured[dev & 63]) {
-        MIO_CUDA(cudaFuncSetAttribute(istft_fast_kernel<N, RADIX...>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        MIO_CUDA(cudaFuncSetAttribute(istft_fast_kernel<FW, N, RADIX...>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
         MIO_CUDA(cudaDeviceGetAttribute(&n_sm[dev & 63], cudaDevAttrMultiProcessorCount, dev));
         configured[dev & 63] = true;
     }
-    // Chunk length = rounds of FW frames minus the 3 halo frames a chunk recomputes.  One CTA per SM: pick the round
+    // Chunk length = rounds of FW frames minus the 3 halo frames a chunk recomputes.  16 / FW CTAs per SM: pick the round
     // count whose CTA total wastes the least in the last wave (cost = waves * rounds).
-    const int sms = std::max(1, n_sm[dev & 63]);
+    const int sms = std::max(1, n_sm[dev & 63]) * (16 / FW);
     long long best_cost = -1;
     int best_rounds = 4;
-    for (int rounds = 2; rounds <= 10; ++rounds) {
+    for (int rounds = 2 * (16 / FW); rounds <= 10 * (16 / FW); ++rounds) {
         const int fpc = rounds * FW - 3;
         long long ctas = 0;
         if (h_frames) for (int u = 0; u < n_utt; ++u) ctas += ((long long) h_frames[u] + 3 + fpc - 1) / fpc;
@@ -426,7 +430,7 @@ void launch_fast_t(fast_params P, const int * h_frames, int n_utt, int max_frame
     const long long n_full_max = (long long) (max_frames - 1) * H + N;
     const long long chunk = (long long) P.frames_per_chunk * H;
     dim3 grid((unsigned) ((n_full_max + chunk - 1) / chunk), (unsigned) n_utt);
-    launch_pdl(istft_fast_kernel<N, RADIX...>, dim3(grid), dim3(FTHREADS), smem, st, P);
+    launch_pdl(istft_fast_kernel<FW, N, RADIX...>, dim3(grid), dim3(FTHREADS), smem, st, P);
     MIO_CUDA(cudaGetLastError());
     count_launch();
 }
@@ -442,16 +446,20 @@ bool launch_istft_fast(const istft_plan & p, const float * spec, int pitch, cons
     fast_params P;
     P.n_freq = p.n_fft / 2 + 1;
     P.pad = (p.n_fft - p.hop) / 2;
-    P.frames_per_chunk = 64 - 3;      // + 3 halo frames = 4 rounds of 16
+    P.frames_per_chunk = 64 - 3;      // (set by launch_fast_t)
+    static const int fw = [] { const char * e = std::getenv("MIO_TTS_B200_ISTFT_FW"); const int v = e ? std::atoi(e) : 8; return v == 16 || v == 4 ? v : 8; }();
     P.tw_m = p.d_tw_m; P.tw_n = p.d_tw_n; P.hann = p.d_hann;
     P.spec = spec; P.pitch = pitch; P.spec_row0 = spec_row0; P.n_frames = n_frames;
     P.audio_off = audio_off; P.audio = audio; P.peak_bits = peak_bits;
     P.scale = 1.0f / (float) P.n_freq;
-    switch (p.n_fft) {
-        case 1920: launch_fast_t<1920, 16, 15, 4>(P, nullptr, n_utt, max_frames, st); break;
-        case 2048: launch_fast_t<2048, 16, 16, 4>(P, nullptr, n_utt, max_frames, st); break;
-        default: launch_fast_t<1280, 16, 10, 4>(P, nullptr, n_utt, max_frames, st); break;
+#define MIO_ISTFT_CASE(FWV)                                                                               \
+    switch (p.n_fft) {                                                                                    \
+        case 1920: launch_fast_t<FWV, 1920, 16, 15, 4>(P, nullptr, n_utt, max_frames, st); break;          \
+        case 2048: launch_fast_t<FWV, 2048, 16, 16, 4>(P, nullptr, n_utt, max_frames, st); break;          \
+        default: launch_fast_t<FWV, 1280, 16, 10, 4>(P, nullptr, n_utt, max_frames, st); break;           \
     }
+    if (fw == 16) { MIO_ISTFT_CASE(16) } else if (fw == 4) { MIO_ISTFT_CASE(4) } else { MIO_ISTFT_CASE(8) }
+#undef MIO_ISTFT_CASE
     return true;
 }
 

@@ -1,23 +1,26 @@
-"""N>1 host logic on CPU: utterance -> rank partitioning (replicas, no data-path collective) and the bench's
-max-over-ranks / sum-over-ranks aggregation, world_size 2 over gloo."""
+"""N>1 host logic on CPU, world_size 2 over gloo: what bench.py does under torchrun besides launching kernels -- each
+rank builds ITS shard of the synthetic workload (benchutil.config2_workload(rank, ...): disjoint seeds, weak scaling),
+and the run is aggregated as time = MAX over ranks, work = SUM over ranks (benchutil.reduce_over_ranks).  There is no
+data-path collective to test: utterances are independent."""
 import os
 import socket
 
 import numpy as np
-import pytest
 
-from mio_tts_cpp_b200.shard import shard_indices, shard_list, unshard
+from mio_tts_cpp_b200 import benchutil as U
 
 
-def test_shard_rule_matches_reference_round_robin():
-    # slot i -> backend_pool[i % n_devices], /root/reference/src/tts-mio-server.cpp:2659-2670
-    assert shard_indices(10, 0, 4) == [0, 4, 8] and shard_indices(10, 3, 4) == [3, 7]
-    assert shard_indices(2, 3, 4) == [] and shard_indices(0, 0, 1) == []
-    items = list("abcdefghij")
-    parts = [shard_list(items, r, 3) for r in range(3)]
-    assert sorted(sum(parts, [])) == items and unshard(parts, len(items)) == items
-    with pytest.raises(ValueError):
-        shard_indices(4, 2, 2)
+def test_rank_shards_are_disjoint_and_reproducible():
+    a0, a1 = U.config2_workload(0, 4, 50), U.config2_workload(1, 4, 50)
+    assert all(x.dtype == np.int32 and x.size == 50 and 0 <= x.min() and x.max() < 12800 for x in a0 + a1)
+    assert not any(np.array_equal(x, y) for x in a0 for y in a1)                 # disjoint seeds per rank
+    assert all(np.array_equal(x, y) for x, y in zip(a0, U.config2_workload(0, 4, 50)))
+    # rank 0 of the multi-GPU run decodes the very batch the single-GPU run decodes (BASELINE config 2, seeds 42..105)
+    assert np.array_equal(U.config2_workload(0, 64, 400)[17], np.random.default_rng(59).integers(0, 12800, 400).astype(np.int32))
+
+
+def test_single_process_reduce_is_identity():
+    assert U.reduce_over_ranks(None, "cpu", 8.5, 1024.0) == (8.5, 1024.0)
 
 
 def _free_port():
@@ -28,25 +31,17 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, n_items, out_dir):
-    import torch
+def _worker(rank, world, port, out_dir):
     import torch.distributed as dist
 
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    lens = [100 + 37 * i for i in range(n_items)]                 # codes per utterance
-    mine = shard_list(lens, rank, world)
-    audio_s = sum(n * 960 / 24000.0 for n in mine)                # what this replica would synthesise
-    step_ms = 10.0 + rank                                          # pretend rank 1 is slower
-    t = torch.tensor([audio_s], dtype=torch.float64)
-    dist.all_reduce(t, op=dist.ReduceOp.SUM)
-    m = torch.tensor([step_ms], dtype=torch.float64)
-    dist.all_reduce(m, op=dist.ReduceOp.MAX)
-    gathered = [None] * world
-    dist.all_gather_object(gathered, [n * 960 for n in mine])     # per-utterance sample counts
+    codes = U.config2_workload(rank, 3 + rank, 100)                 # ragged on purpose: rank 1 has one utterance more
+    audio_s = sum(c.size * 960 / 24000.0 for c in codes)
+    ms, total = U.reduce_over_ranks(dist, "cpu", 10.0 + rank, audio_s)      # pretend rank 1 is slower
     if rank == 0:
-        np.save(os.path.join(out_dir, "res.npy"), np.array([t.item(), m.item()] + unshard(gathered, n_items)))
+        np.save(os.path.join(out_dir, "res.npy"), np.array([ms, total]))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -54,10 +49,7 @@ def _worker(rank, world, port, n_items, out_dir):
 def test_two_rank_replicas_aggregate(tmp_path):
     import torch.multiprocessing as mp
 
-    n_items, world = 7, 2
-    mp.spawn(_worker, args=(world, _free_port(), n_items, str(tmp_path)), nprocs=world, join=True)
-    res = np.load(tmp_path / "res.npy")
-    lens = [100 + 37 * i for i in range(n_items)]
-    assert np.isclose(res[0], sum(n * 960 / 24000.0 for n in lens))      # whole-job audio seconds
-    assert res[1] == 11.0                                               # time = max over ranks
-    assert res[2:].tolist() == [n * 960 for n in lens]                  # original utterance order restored
+    mp.spawn(_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    ms, total = np.load(tmp_path / "res.npy")
+    assert ms == 11.0                                               # time = max over ranks
+    assert np.isclose(total, (3 + 4) * 100 * 960 / 24000.0)         # whole-job audio seconds = sum over ranks
