@@ -86,6 +86,11 @@ enum gemm_epilogue : int {
     EPI_STORE16 = 1,   // out16[r,n] = acc + bias[n]
     EPI_SWIGLU16 = 2,  // out16[r,n/2] = silu(acc[r,2j]) * acc[r,2j+1]   (weights interleaved gate/up)
     EPI_ROPE16 = 3,    // out16[r,n] = rope(acc) for n < rope_cols (q,k); plain for v
+    // EPI_STORE32 with the in-place residual, FOLLOWED BY THE LAYERNORM THAT CONSUMES IT, in one kernel (N == 512 only):
+    //   x[r,:] = (acc + bias) * gate + x[r,:]  (fp32, map_out);  out16_2[r,:] = LN(x[r,:]) * A + B  (16-bit, map_out2)
+    // A CTA pair owns whole rows (both 256-column accumulators of its TMEM), writes x back into TMEM, takes the row
+    // statistics there and emits the next GEMM's A operand: the LayerNorm launch and its re-read of x disappear.
+    EPI_STORE32_LN = 4,
 };
 
 struct gemm_args {
@@ -117,6 +122,10 @@ struct gemm_args {
     // a separate pass over the output.  Needs row_utt, N % 32 == 0 and N / gn_groups == 16 or a multiple of 32.
     double * gn_stats; int gn_groups;
     int reverse_m;                       // walk the row tiles from the last to the first (ping-pong traversal): set by gemm_launch
+    // EPI_STORE32_LN: y = (x - mean) * rstd, out2 = y * (ln_plus1 + A[n]) + B[n] with A = ln_a + utt * ln_ld, B = ln_b + utt * ln_ld
+    // (AdaLN: per-utterance scale / shift, ln_plus1 = 1; plain LayerNorm: ln_ld = 0, ln_plus1 = 0); gap rows (utt < 0) -> 0
+    CUtensorMap map_out2;                // [rows, N] 16-bit, box 32 x 32, swizzle 64B
+    const float * ln_a; const float * ln_b; int ln_ld; float ln_plus1; float ln_eps; int ln_out_dtype;
 };
 inline bool gemm_gn_stats_ok(int N, int groups) {
     if (groups <= 0 || N % groups != 0 || N % 32 != 0) return false;

@@ -413,12 +413,17 @@ void engine::flip() { set_traversal_reverse(dir_ ^= 1); }
 
 void engine::gemm(const dbuf & a, const dev_linear & w, int M, int epilogue, void * out, int ldo, int out_dtype,
                   const float * bias, const float * res, int ldr, const float * gate, const seq_layout * lay,
-                  const float2 * rope, int heads, double * gn_stats, int gn_groups) {
+                  const float2 * rope, int heads, double * gn_stats, int gn_groups, const ln_fuse * ln) {
     gemm_args g;
     std::memset(&g, 0, sizeof(g));
+    if (ln != nullptr) {        // EPI_STORE32_LN: the LayerNorm that consumes this GEMM's output, emitted as 16-bit rows
+        g.map_out2 = omap(ln->out16, M, w.N, w.N, 2);
+        g.ln_a = ln->a; g.ln_b = ln->b; g.ln_ld = ln->ld; g.ln_plus1 = ln->plus1; g.ln_eps = mdl->hp.norm_eps;
+        g.ln_out_dtype = ln->out_dtype;
+    }
     g.map_a = amap(a, w.K);
     g.map_b = w.map_b;
-    g.map_out = omap(out, M, epilogue == EPI_SWIGLU16 ? w.N / 2 : w.N, ldo, epilogue == EPI_STORE32 ? 4 : 2);
+    g.map_out = omap(out, M, epilogue == EPI_SWIGLU16 ? w.N / 2 : w.N, ldo, (epilogue == EPI_STORE32 || epilogue == EPI_STORE32_LN) ? 4 : 2);
     g.M = M; g.N = w.N; g.K = w.K; g.taps = w.taps;
     g.tap_row0 = -(w.taps >> 1);   // k=3 "same" convolution over rows (taps == 1: plain GEMM)
     g.dtype = w.dtype; g.out_dtype = out_dtype; g.epilogue = epilogue;
@@ -444,24 +449,50 @@ void engine::gemm(const dbuf & a, const dev_linear & w, int M, int epilogue, voi
         gemm_ev_flops_.push_back({evi, 2.0 * (double) (lay ? lay->valid : M) * w.N * w.K * w.taps});
         // algorithmic DRAM bytes of this launch: A once (the taps re-read the same rows), W once, the output, the residual
         const double out_cols = epilogue == EPI_SWIGLU16 ? w.N / 2 : w.N;
-        gemm_bytes_ += (double) M * w.K * 2 + (double) w.N * w.K * w.taps * 2 + (double) M * out_cols * (epilogue == EPI_STORE32 ? 4 : 2) +
-                       (res ? (double) M * w.N * 4 : 0.0);
+        gemm_bytes_ += (double) M * w.K * 2 + (double) w.N * w.K * w.taps * 2 +
+                       (double) M * out_cols * ((epilogue == EPI_STORE32 || epilogue == EPI_STORE32_LN) ? 4 : 2) +
+                       (res ? (double) M * w.N * 4 : 0.0) + (ln ? (double) M * w.N * 2 : 0.0);
         gemm_ev_shape_.push_back({M, w.N, w.K, w.taps, epilogue});
     }
 }
 
-void engine::run_tblock(float * x, const seq_layout & L, const tblock & blk, int dim, int heads, int ff, int window,
-                        const float2 * rope, bool cond) {
+// One transformer block.  ln1_done: the block's first LayerNorm already sits in act16_ (emitted by the previous block's
+// down-projection).  next: the block whose first LayerNorm this block's down-projection should emit (nullptr: none).
+// With dim == 512 (the AdaLN decoder) the O-projection emits the block's second LayerNorm the same way, so a fused block
+// launches no LayerNorm kernel at all (MIO_TTS_B200_LN_FUSE=0 restores the separate kernels).
+bool engine::run_tblock(float * x, const seq_layout & L, const tblock & blk, int dim, int heads, int ff, int window,
+                        const float2 * rope, bool cond, bool ln1_done, const tblock * next) {
+    static const bool fuse_env = [] { const char * e = std::getenv("MIO_TTS_B200_LN_FUSE"); return !(e && e[0] == '0'); }();
     const hparams & hp = mdl->hp;
     const int rows = L.rows;
     const int ldt = mdl->linear_dtype;
     const float * cv = (const float *) cond_.p;
-    if (cond)
-        { flip(); launch_layernorm(x, rows, dim, hp.norm_eps, nullptr, nullptr, cv, mdl->cond_total, blk.cond_attn_off,
-                         blk.cond_attn_off + dim, L.d_row_utt, act16_.p, ldt, nullptr, st_); }
-    else
-        { flip(); launch_layernorm(x, rows, dim, hp.norm_eps, blk.ln1.w, blk.ln1.b, nullptr, 0, 0, 0, L.d_row_utt, act16_.p, ldt,
-                         nullptr, st_); }
+    const bool fuse = fuse_env && dim == 512 && (blk.o.K % 64) == 0 && (blk.down.K % 64) == 0;
+    // LayerNorm parameters as the fused epilogue wants them: AdaLN (scale, shift) rows of the utterance, or (weight, bias)
+    auto ln_params = [&](const tblock & b, bool second) {
+        ln_fuse f;
+        f.out16 = act16_.p; f.out_dtype = ldt;
+        if (cond) {
+            const int off = second ? b.cond_ffn_off : b.cond_attn_off;
+            f.a = cv + off + dim; f.b = cv + off; f.ld = mdl->cond_total; f.plus1 = 1.0f;
+        } else {
+            const dev_norm & n = second ? b.ln2 : b.ln1;
+            f.a = n.w; f.b = n.b; f.ld = 0; f.plus1 = 0.0f;
+        }
+        return f;
+    };
+    auto ln_launch = [&](const tblock & b, bool second) {
+        flip();
+        if (cond) {
+            const int off = second ? b.cond_ffn_off : b.cond_attn_off;
+            launch_layernorm(x, rows, dim, hp.norm_eps, nullptr, nullptr, cv, mdl->cond_total, off, off + dim, L.d_row_utt, act16_.p,
+                             ldt, nullptr, st_);
+        } else {
+            const dev_norm & n = second ? b.ln2 : b.ln1;
+            launch_layernorm(x, rows, dim, hp.norm_eps, n.w, n.b, nullptr, 0, 0, 0, L.d_row_utt, act16_.p, ldt, nullptr, st_);
+        }
+    };
+    if (!ln1_done) ln_launch(blk, false);
     gemm(act16_, blk.qkv, rows, EPI_ROPE16, qkv16_.p, 3 * dim, ldt, nullptr, nullptr, 0, nullptr, &L, rope, heads);
     size_t evi = 0;
     if (prof_gemm_) {
@@ -469,24 +500,33 @@ void engine::run_tblock(float * x, const seq_layout & L, const tblock & blk, int
         while (gemm_ev_.size() < evi + 2) { cudaEvent_t e; MIO_CUDA(cudaEventCreate(&e)); gemm_ev_.push_back(e); }
         MIO_CUDA(cudaEventRecord(gemm_ev_[evi], st_));
     }
+    flip();
     if (!force_generic_attention && attention_tc_ok(dim, heads, window))
-        { flip(); launch_attention_tc(xmap(qkv16_.p, rows, 3 * dim, 128), xmap(qkv16_.p, rows, 3 * dim, 192), xmap(att16_.p, rows, dim, 32),
-                            att16_.p, ldt, dim, heads, window, rows, L.d_tiles128, L.n_tiles128, mdl->num_sms, st_); }
+        launch_attention_tc(xmap(qkv16_.p, rows, 3 * dim, 128), xmap(qkv16_.p, rows, 3 * dim, 192), xmap(att16_.p, rows, dim, 32),
+                            att16_.p, ldt, dim, heads, window, rows, L.d_tiles128, L.n_tiles128, mdl->num_sms, st_);
     else if (!force_generic_attention && attention_tma_ok(dim, heads, window))
-        { flip(); launch_attention_tma(xmap(qkv16_.p, rows, 3 * dim, 64), xmap(att16_.p, rows, dim, 16), att16_.p, ldt, dim, heads, window,
-                             rows, L.d_tiles, L.n_tiles, mdl->num_sms, st_); }
+        launch_attention_tma(xmap(qkv16_.p, rows, 3 * dim, 64), xmap(att16_.p, rows, dim, 16), att16_.p, ldt, dim, heads, window,
+                             rows, L.d_tiles, L.n_tiles, mdl->num_sms, st_);
     else
-        { flip(); launch_attention(qkv16_.p, att16_.p, ldt, dim, heads, window, L.d_tiles, L.n_tiles, force_generic_attention, st_); }
+        launch_attention(qkv16_.p, att16_.p, ldt, dim, heads, window, L.d_tiles, L.n_tiles, force_generic_attention, st_);
     if (prof_gemm_) { MIO_CUDA(cudaEventRecord(gemm_ev_[evi + 1], st_)); attn_ev_.push_back(evi); }
-    gemm(att16_, blk.o, rows, EPI_STORE32, x, dim, 0, nullptr, x, dim, cond ? cv + blk.cond_attn_off + 2 * dim : nullptr, &L);
-    if (cond)
-        { flip(); launch_layernorm(x, rows, dim, hp.norm_eps, nullptr, nullptr, cv, mdl->cond_total, blk.cond_ffn_off,
-                         blk.cond_ffn_off + dim, L.d_row_utt, act16_.p, ldt, nullptr, st_); }
-    else
-        { flip(); launch_layernorm(x, rows, dim, hp.norm_eps, blk.ln2.w, blk.ln2.b, nullptr, 0, 0, 0, L.d_row_utt, act16_.p, ldt,
-                         nullptr, st_); }
+    const float * gate1 = cond ? cv + blk.cond_attn_off + 2 * dim : nullptr;
+    const float * gate2 = cond ? cv + blk.cond_ffn_off + 2 * dim : nullptr;
+    if (fuse) {
+        const ln_fuse f2 = ln_params(blk, true);
+        gemm(att16_, blk.o, rows, EPI_STORE32_LN, x, dim, 0, nullptr, x, dim, gate1, &L, nullptr, 0, nullptr, 0, &f2);
+    } else {
+        gemm(att16_, blk.o, rows, EPI_STORE32, x, dim, 0, nullptr, x, dim, gate1, &L);
+        ln_launch(blk, true);
+    }
     gemm(act16_, blk.gate_up, rows, EPI_SWIGLU16, ff16_.p, ff, ldt, nullptr, nullptr, 0, nullptr, &L);
-    gemm(ff16_, blk.down, rows, EPI_STORE32, x, dim, 0, nullptr, x, dim, cond ? cv + blk.cond_ffn_off + 2 * dim : nullptr, &L);
+    if (fuse && next != nullptr) {
+        const ln_fuse f1 = ln_params(*next, false);
+        gemm(ff16_, blk.down, rows, EPI_STORE32_LN, x, dim, 0, nullptr, x, dim, gate2, &L, nullptr, 0, nullptr, 0, &f1);
+        return true;
+    }
+    gemm(ff16_, blk.down, rows, EPI_STORE32, x, dim, 0, nullptr, x, dim, gate2, &L);
+    return false;
 }
 
 // GroupNorm + SiLU -> 16-bit conv operand.  The per-(utterance, group) sums of slot `slot` either were accumulated by the
@@ -616,8 +656,12 @@ void engine::run_direct(bool with_istft, stage_times * prof, int stop_stage) {
     // ---- prenet: gather -> transformer blocks -> LN -> linear (src/miocodec-decoder.cpp:1357-1365) ----
     float * xt = (float *) xt_.p;
     launch_gather(mdl->tok_embd, d_codes_, xt, tok_.rows, pd, st_);
-    for (const tblock & b : mdl->prenet)
-        run_tblock(xt, tok_, b, pd, hp.prenet_heads, hp.prenet_ff, hp.prenet_window, rope_p_, false);
+    {
+        bool ln_done = false;
+        for (size_t i = 0; i < mdl->prenet.size(); ++i)
+            ln_done = run_tblock(xt, tok_, mdl->prenet[i], pd, hp.prenet_heads, hp.prenet_ff, hp.prenet_window, rope_p_, false, ln_done,
+                                 i + 1 < mdl->prenet.size() ? &mdl->prenet[i + 1] : nullptr);
+    }
     flip();
     launch_layernorm(xt, tok_.rows, pd, hp.norm_eps, mdl->prenet_norm.w, mdl->prenet_norm.b, nullptr, 0, 0, 0,
                      tok_.d_row_utt, act16_.p, ldt, nullptr, st_);
@@ -639,8 +683,12 @@ void engine::run_direct(bool with_istft, stage_times * prof, int stop_stage) {
     if (stop(3, fx, dd, 0, 0, &frm_)) return;
 
     // ---- AdaLN-Zero decoder (:1382-1400) ----
-    for (const tblock & b : mdl->decoder)
-        run_tblock(fx, frm_, b, dd, hp.decoder_heads, hp.decoder_ff, hp.decoder_window, rope_d_, hp.dynamic_global);
+    {
+        bool ln_done = false;
+        for (size_t i = 0; i < mdl->decoder.size(); ++i)
+            ln_done = run_tblock(fx, frm_, mdl->decoder[i], dd, hp.decoder_heads, hp.decoder_ff, hp.decoder_window, rope_d_,
+                                 hp.dynamic_global, ln_done, i + 1 < mdl->decoder.size() ? &mdl->decoder[i + 1] : nullptr);
+    }
     if (hp.dynamic_global)
         { flip(); launch_layernorm(fx, frm_.rows, dd, hp.norm_eps, nullptr, nullptr, (const float *) cond_.p, mdl->cond_total,
                          mdl->cond_final_off, mdl->cond_final_off + dd, frm_.d_row_utt, nullptr, 0, fy, st_); }

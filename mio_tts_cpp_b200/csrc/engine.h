@@ -24,6 +24,11 @@ struct seq_layout {
     size_t off_len = 0, off_row0 = 0, off_row_utt = 0, off_row_pos = 0, off_tiles = 0, off_tiles128 = 0;   // offsets in the metadata blob
 };
 
+struct ln_fuse {      // the LayerNorm an EPI_STORE32_LN GEMM emits: out16 = LN(x) * (plus1 + a[utt * ld + n]) + b[utt * ld + n]
+    void * out16 = nullptr; int out_dtype = 0;
+    const float * a = nullptr, * b = nullptr; int ld = 0; float plus1 = 0.0f;
+};
+
 struct dbuf {
     void * p = nullptr;
     size_t cap = 0;
@@ -136,9 +141,10 @@ private:
 
     void gemm(const dbuf & a, const dev_linear & w, int M, int epilogue, void * out, int ldo, int out_dtype,
               const float * bias, const float * res, int ldr, const float * gate, const seq_layout * lay,
-              const float2 * rope = nullptr, int heads = 0, double * gn_stats = nullptr, int gn_groups = 0);
-    void run_tblock(float * x, const seq_layout & L, const tblock & blk, int dim, int heads, int ff, int window,
-                    const float2 * rope, bool cond);
+              const float2 * rope = nullptr, int heads = 0, double * gn_stats = nullptr, int gn_groups = 0,
+              const ln_fuse * ln = nullptr);
+    bool run_tblock(float * x, const seq_layout & L, const tblock & blk, int dim, int heads, int ff, int window,
+                    const float2 * rope, bool cond, bool ln1_done, const tblock * next);
     bool run_resblock(float *& x, float *& y, const seq_layout & L, const resblock & rb, int & gn_slot, bool in_ready,
                       bool feeds_next);
     void group_norm_silu(const float * x, const seq_layout & L, int channels, int groups, const dev_norm & n, int slot,

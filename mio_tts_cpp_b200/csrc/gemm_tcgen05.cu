@@ -737,6 +737,8 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
     }
 }
 
+#include "gemm_ln.inc"
+
 typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                     const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
                                     CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -882,6 +884,13 @@ void gemm_launch(const gemm_args & a, int num_sms, cudaStream_t st) {
     }
     gemm_args g = a;
     g.reverse_m = traversal_reverse();
+    if (a.epilogue == EPI_STORE32_LN) {
+        if (a.N != 512 || a.taps != 1 || a.res == nullptr || a.ln_a == nullptr || a.ln_b == nullptr || (a.K % BLOCK_K) != 0 ||
+            a.gn_stats != nullptr || (a.gate != nullptr && a.row_utt == nullptr))
+            throw cuda_error("gemm: the LayerNorm-fused epilogue needs N = 512, one tap, the in-place residual and LN parameters");
+        launch_ln(g, num_sms, st);
+        return;
+    }
     if (g.gn_stats != nullptr && (a.epilogue != EPI_STORE32 || a.row_utt == nullptr || a.bias == nullptr || a.gate != nullptr ||
                                   !gemm_gn_stats_ok(a.N, a.gn_groups)))
         throw cuda_error("gemm: GroupNorm statistics need the fp32-store epilogue with bias, row_utt, no gate, and a supported group width");
