@@ -41,5 +41,28 @@ def main():
         print(f"{i:5d} {100 * s / max(1, tot):5.1f}%  exec={r['Instructions Executed']:>9}  {r['Source'][:90]:90s} {why[0][1]}:{why[0][0]} {why[1][1]}:{why[1][0]}")
 
 
+def window(rep, lo, hi, which=0):
+    """SASS lines lo..hi of the source page with their sample counts (to read the code around a hot spot)."""
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+    blocks, cur = [], []
+    for line in raw.splitlines():
+        if line.startswith('"Kernel Name"'):
+            if cur:
+                blocks.append(cur)
+            cur = [line]
+        elif cur:
+            cur.append(line)
+    if cur:
+        blocks.append(cur)
+    rows = list(csv.DictReader(io.StringIO("\n".join(blocks[which][1:]))))
+    for i in range(max(0, lo), min(len(rows), hi)):
+        r = rows[i]
+        print(f"{i:5d} {int(r['# Samples'] or 0):6d}  exec={r['Instructions Executed']:>9}  {r['Source'][:110]}")
+
+
+if __name__ == "__main__" and len(sys.argv) > 2 and sys.argv[2] == "window":
+    window(sys.argv[1], int(sys.argv[3]), int(sys.argv[4]))
+    sys.exit(0)
+
 if __name__ == "__main__":
     main()
