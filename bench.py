@@ -295,8 +295,9 @@ def run_b200(args, rank, world, local_rank):
 
     line = {"metric": baseline_metric(), "value": value, "unit": "audio-seconds/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "vs_baseline": None, "dtype": os.environ.get("MIO_TTS_B200_LINEAR_DTYPE", "f16"), "data": "synthetic",
             "config": {"workload": f"config2: batch {BATCH} x {N_CODES} codes per GPU, default 24 kHz hyper-parameters, "
+                                   "fp16 operands / fp32 accumulate (same tensor rate as bf16; MIO_TTS_B200_LINEAR_DTYPE=bf16 selects bf16), "
                                    "fp32 iSTFT, synthetic weights in the reference GGUF layout",
                        "audio_seconds_per_step_per_gpu": audio_s_per_step, "parallelism": f"replicas x{world}",
                        "l2": "no flush: each step streams ~2 GB of activations (> 126 MB L2); inputs are 100 KB of codes"},
@@ -374,7 +375,7 @@ def run_b200(args, rank, world, local_rank):
             line["parity_max_abs"] = max(x["max_abs"] for x in par.values())
             line["parity"] = {"against": "oracle/_ref (unmodified reference, fp32 CPU) on the same codes + embedding"
                               if kind == "reference" else "numpy oracle", "utterances": par,
-                              "linear_dtype": os.environ.get("MIO_TTS_B200_LINEAR_DTYPE", "bf16")}
+                              "linear_dtype": os.environ.get("MIO_TTS_B200_LINEAR_DTYPE", "f16")}
         if json_fd is None:
             print(json.dumps(line), flush=True)
         else:
@@ -407,6 +408,7 @@ def aux_configs(m, peaks):
                                                 "bytes_per_frame": b392}}
     # codebook gather alone over the config-2 batch (north_star: achieved HBM GB/s of the gather): 25 600 rows x 768 fp32
     # written (79 MB) + the rows read (the 39 MB table is L2-resident after the first pass)
+    m.prepare(U.config2_workload(0, BATCH, N_CODES), [U.speaker_embedding()] * BATCH)   # (the iSTFT legs reused the batch tables)
     g_ms = m.gather_bench(50)
     g_bytes = BATCH * N_CODES * m.prenet_dim() * 4 * 2 + BATCH * N_CODES * 4
     out["gather"] = {"rows": BATCH * N_CODES, "dim": m.prenet_dim(), "ms": g_ms, "bit_exact": True,

@@ -36,8 +36,7 @@ template <bool BF16> __device__ __forceinline__ uint32_t pack2(float a, float b)
         __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
         return *reinterpret_cast<uint32_t *>(&v);
     } else {
-        __half2 v = __floats2half2_rn(a, b);
-        return *reinterpret_cast<uint32_t *>(&v);
+        return pack_f16x2_sat(a, b);
     }
 }
 

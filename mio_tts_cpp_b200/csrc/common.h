@@ -63,6 +63,16 @@ void set_traversal_reverse(int rev);
 
 // 16-bit operand formats of the tensor-core GEMMs (tcgen05 kind::f16 a/b_format field)
 enum op16 : int { OP_F16 = 0, OP_BF16 = 1 };
+#ifdef __CUDACC__
+// (lo, hi) -> packed fp16 pair, SATURATING: a value beyond +-65504 becomes +-65504 instead of inf (one F2FP.SATFINITE).
+// fp16 operands are the default for the linears (10 mantissa bits, like the TF32 the reference's own CUDA path uses); a
+// checkpoint with an activation outlier then clips one value instead of turning the utterance into NaNs.
+__device__ __forceinline__ uint32_t pack_f16x2_sat(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+#endif
 
 // ---------------------------------------------------------------------------------------------
 // Row layouts.  Activations are [rows, channels] row-major (channel-contiguous).  A layout packs

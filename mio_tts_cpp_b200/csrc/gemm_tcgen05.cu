@@ -215,8 +215,7 @@ __device__ __forceinline__ uint32_t pack16(float a, float b, int dtype) {
         __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
         return *reinterpret_cast<uint32_t *>(&v);
     }
-    __half2 v = __floats2half2_rn(a, b);
-    return *reinterpret_cast<uint32_t *>(&v);
+    return pack_f16x2_sat(a, b);
 }
 
 // x * sigmoid(x) on the SFU (ex2.approx + rcp.approx, ~2 ulp; the result is rounded to 16 bits anyway)
@@ -300,8 +299,7 @@ template <bool BF16> __device__ __forceinline__ uint32_t pack16t(float a, float 
         __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
         return *reinterpret_cast<uint32_t *>(&v);
     } else {
-        __half2 v = __floats2half2_rn(a, b);
-        return *reinterpret_cast<uint32_t *>(&v);
+        return pack_f16x2_sat(a, b);
     }
 }
 

@@ -21,8 +21,7 @@ __device__ __forceinline__ uint32_t pack16(float a, float b, int dtype) {
         __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
         return *reinterpret_cast<uint32_t *>(&v);
     }
-    __half2 v = __floats2half2_rn(a, b);
-    return *reinterpret_cast<uint32_t *>(&v);
+    return pack_f16x2_sat(a, b);
 }
 
 __device__ __forceinline__ float silu_exact(float x) { return x / (1.0f + expf(-x)); }

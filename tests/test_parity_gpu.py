@@ -3,10 +3,11 @@
 Tolerances (BASELINE.json north_star):
   * codebook gather: bit-exact.
   * fp32 iSTFT fed the oracle's / reference's spectrogram: max-abs <= 1e-3 and SNR >= 40 dB (measured: > 110 dB).
-  * decoder in bf16 operands / fp32 accumulate (fp16 operands for the convs, as the reference rounds them):
-    spectrogram SNR >= 38 dB vs the reference's fp32 CPU decode (measured 41-47 dB on the six fixtures) and end-to-end
-    waveform SNR >= 28 dB (measured 30-38 dB; the phase half of the spectrogram amplifies operand rounding).
-    With MIO_TTS_B200_LINEAR_DTYPE=f16 the same path measures higher; that mode is checked in a subprocess.
+  * decoder with fp16 operands / fp32 accumulate (the default: linears AND convs -- the reference rounds its conv
+    operands to fp16 itself): spectrogram SNR >= SPEC_SNR_MIN vs the reference's fp32 CPU decode and end-to-end waveform
+    SNR >= AUDIO_SNR_MIN (the phase half of the spectrogram amplifies operand rounding); measured values are printed.
+    MIO_TTS_B200_LINEAR_DTYPE=bf16 (bf16 linears: 3 mantissa bits fewer, fp32's range) is checked in a subprocess
+    against the looser gates it was built to: >= 38 dB / >= 28 dB.
 """
 import os
 import subprocess
@@ -21,7 +22,7 @@ from oracle import miocodec_np as O
 
 pytestmark = pytest.mark.gpu
 
-SPEC_SNR_MIN, AUDIO_SNR_MIN = 38.0, 28.0
+SPEC_SNR_MIN, AUDIO_SNR_MIN = 54.0, 44.0      # measured: spec 58-66 dB, audio 48-58 dB (400 codes: 61 / 52 dB)
 
 
 @pytest.fixture(scope="module")
@@ -107,6 +108,7 @@ def test_decode_and_synthesize_vs_reference_fixture(name, ctxs, gguf_paths, emb)
     emb = case_embedding(z, emb)
     spec = m.decode_spec(z["codes"], emb)
     assert spec.shape == z["spec"].shape and np.isfinite(spec).all()
+    print(f"{name}: spec {snr_db(spec, z['spec']):.1f} dB")
     assert snr_db(spec, z["spec"]) >= SPEC_SNR_MIN
     # the fp32 iSTFT on the REFERENCE's spectrogram reproduces the reference's waveform (before peak normalise)
     hp = O.Model(gguf_paths(preset)[0]).hp
@@ -118,6 +120,7 @@ def test_decode_and_synthesize_vs_reference_fixture(name, ctxs, gguf_paths, emb)
     assert sr == int(z["sample_rate"]) and audio.shape == ref_audio.shape
     if m.samples_per_token() % hp["hop_length"] == 0:
         assert audio.size == z["codes"].size * m.samples_per_token()
+    print(f"{name}: audio {snr_db(audio, ref_audio):.1f} dB")
     assert snr_db(audio, ref_audio) >= AUDIO_SNR_MIN
 
 
@@ -147,6 +150,7 @@ def test_full_size_vs_reference_fixture(ctxs, gguf_paths, emb):
         b_db = snr_db(full_case_audio_windows(z, batch[u]), z["audio"])
         print(f"{name}: spec {s_db:.1f} dB, audio {a_db:.1f} dB, in batch {b_db:.1f} dB")
         assert s_db >= SPEC_SNR_MIN and a_db >= AUDIO_SNR_MIN and b_db >= AUDIO_SNR_MIN
+        assert np.abs(full_case_audio_windows(z, audio) - z["audio"]).max() <= 1e-3
         assert batch[u].tobytes() == audio.tobytes()
         # the fp32 iSTFT alone, fed the reference's rows where the fixture kept them, cannot be checked on a strided
         # spectrogram; the waveform peak rule can: the reference's peak after normalisation
@@ -165,7 +169,7 @@ def test_full_size_stages_vs_oracle(ctxs, gguf_paths, emb):
         assert got.shape == st[k].shape
         db = snr_db(got, st[k])
         print(f"stage {k}: {db:.1f} dB")
-        assert db >= 36.0, k
+        assert db >= 52.0, k      # measured 58.3-61.5 dB
     spec = m.decode_spec(codes, emb)
     assert snr_db(spec, ref_spec) >= SPEC_SNR_MIN
     audio, _ = m.synthesize(codes, emb)
@@ -193,6 +197,8 @@ def test_full_size_vs_live_reference(ctxs, gguf_paths, emb):
             db = snr_db(audio, ref_audio)
             print(f"live reference seed {seed} T {T}: audio {db:.1f} dB, max abs {np.abs(audio - ref_audio).max():.2e}")
             assert db >= AUDIO_SNR_MIN
+            # north_star's waveform tolerance (max-abs 1e-3, >= 40 dB), stated there for the fp32 iSTFT, holds end to end
+            assert np.abs(audio - ref_audio).max() <= 1e-3
     finally:
         R.close_context(ctx)
 
@@ -227,7 +233,7 @@ def test_intermediate_stages_vs_oracle(name, stage_keys, ctxs, gguf_paths, emb):
     for i, k in enumerate(stage_keys, start=1):
         got = ctxs(preset).debug_stage(z["codes"], emb, i)
         assert got.shape == st[k].shape
-        assert snr_db(got, st[k]) >= 36.0, k      # measured 40.0-47.5 dB
+        assert snr_db(got, st[k]) >= 52.0, k      # measured 58-64 dB
 
 
 def test_generic_attention_agrees_with_band_kernel(ctxs, emb):
@@ -366,23 +372,27 @@ def test_backend_device_switch(ctxs, emb):
         m.free()
 
 
-def test_f16_linear_mode_is_closer(gguf_paths, emb):
-    """MIO_TTS_B200_LINEAR_DTYPE=f16: fp16 operands for the linears too (10 mantissa bits, like the reference's own
-    TF32 CUDA path).  Run in a subprocess because the mode is read at model load."""
+def test_bf16_linear_mode(gguf_paths, emb):
+    """MIO_TTS_B200_LINEAR_DTYPE=bf16: bf16 operands for the linears (the round-1 default; fp32's exponent range for
+    checkpoints whose activations would saturate fp16).  Run in a subprocess because the mode is read at model load; gated
+    at the tolerance that mode was built to, at 24 and at 400 codes."""
     path = gguf_paths("default")[0]
     code = (
         "import sys, numpy as np; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
-        "from conftest import load_golden, snr_db\n"
+        "from conftest import load_golden, snr_db, full_case_audio_windows\n"
         "from mio_tts_cpp_b200 import MioTTS\n"
-        "z = load_golden('default_T24'); emb = np.load(%r)\n"
-        "m = MioTTS(%r); s = m.decode_spec(z['codes'], emb); a, _ = m.synthesize(z['codes'], emb)\n"
+        "emb = np.load(%r); m = MioTTS(%r)\n"
+        "z = load_golden('default_T24'); s = m.decode_spec(z['codes'], emb); a, _ = m.synthesize(z['codes'], emb)\n"
         "print('SNR', snr_db(s, z['spec']), snr_db(a, z['audio']))\n"
+        "z = load_golden('default_T400'); s = m.decode_spec(z['codes'], emb); a, _ = m.synthesize(z['codes'], emb)\n"
+        "print('SNR', snr_db(s[::int(z['spec_stride'])], z['spec']), snr_db(full_case_audio_windows(z, a), z['audio']))\n"
     ) % (ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "tests", "golden", "en_female_emb.npy"), path)
-    env = dict(os.environ, MIO_TTS_B200_LINEAR_DTYPE="f16")
+    env = dict(os.environ, MIO_TTS_B200_LINEAR_DTYPE="bf16")
     out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stderr[-2000:]
-    line = [ln for ln in out.stdout.splitlines() if ln.startswith("SNR")][-1].split()
-    assert float(line[1]) >= 50.0 and float(line[2]) >= 40.0, line
+    lines = [ln.split() for ln in out.stdout.splitlines() if ln.startswith("SNR")]
+    print("bf16 linears:", lines)
+    assert len(lines) == 2 and all(float(ln[1]) >= 38.0 and float(ln[2]) >= 28.0 for ln in lines), lines
 
 
 def test_gemm_tail_split_is_bit_invariant(gguf_paths, emb):
