@@ -190,6 +190,25 @@ MIO_B200_API bool mio_tts_b200_batching_stats(struct mio_tts_context * ctx, uint
 MIO_B200_API bool mio_tts_b200_audio_to_pcm16(struct mio_tts_context * ctx, const float * const * audio, const size_t * n_audio,
                                               size_t batch, int16_t ** pcm_out, char * err, size_t err_size);
 
+/* The same WAV16 conversion (peak rule + clamp + round) for callers that cannot allocate: code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc.  This entry point has NO counterpart in the reference.
+ * It calls no cudaMalloc / cudaFree / allocating library routine and takes
+ * no host heap memory: its scratch (per-utterance peak words and the offset / length tables) is a file-scope __device__
+ * array of MIO_TTS_B200_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit.
+ *   d_audio  DEVICE pointer: utterance u = lengths[u] float samples at d_audio + offsets[u] (un-normalised waveform)
+ *   d_pcm    DEVICE pointer: receives utterance u's int16 samples at d_pcm + offsets[u]
+ *   offsets / lengths  HOST arrays of `batch` entries (samples); batch <= MIO_TTS_B200_STATIC_MAX_UTT, else the call
+ *            fails with "... exceeds the static scratch ..."
+ *   device   CUDA device ordinal that owns d_audio / d_pcm;  stream: a cudaStream_t of that device, or NULL
+ * All calls of a process share the one array per GPU and it keeps the last call's contents (the peak words are cleared
+ * at the start of every call).  Two calls that overlap on the GPU would race on it: the library therefore serialises
+ * the callers of a process with a mutex and returns only after the stream has drained. */
+#define MIO_TTS_B200_STATIC_MAX_UTT 2048
+#define MIO_TTS_B200_STATIC_SCRATCH_BYTES (MIO_TTS_B200_STATIC_MAX_UTT * 20)
+MIO_B200_API bool mio_tts_b200_pcm16_static(int32_t device, const float * d_audio, const int64_t * offsets,
+                                            const int64_t * lengths, size_t batch, int16_t * d_pcm, void * stream,
+                                            char * err, size_t err_size);
+
 /* Stage hooks for parity tests.  decode_spec mirrors miocodec_decoder::decode_tokens
  * (/root/reference/src/miocodec-decoder.cpp:1079): spec_out = malloc'd [n_frames][n_bins]. */
 MIO_B200_API bool mio_tts_b200_decode_spec(struct mio_tts_context * ctx, const int32_t * codes, size_t n_codes,

@@ -85,6 +85,7 @@ def load_library():
         "mio_tts_b200_context_enable_batching": (C.c_bool, [vp, i32, i32, i32, cp, sz]),
         "mio_tts_b200_batching_stats": (C.c_bool, [vp, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]),
         "mio_tts_b200_audio_to_pcm16": (C.c_bool, [vp, C.POINTER(fp), szp, sz, C.POINTER(C.POINTER(C.c_int16)), cp, sz]),
+        "mio_tts_b200_pcm16_static": (C.c_bool, [i32, vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64), sz, vp, vp, cp, sz]),
         "mio_tts_b200_decode_spec": (C.c_bool, [vp, ip, sz, fp, sz, fpp, ip, ip, cp, sz]),
         "mio_tts_b200_debug_stage": (C.c_bool, [vp, ip, sz, fp, sz, i32, fpp, ip, ip, cp, sz]),
         "mio_tts_b200_gather": (C.c_bool, [vp, ip, sz, fp, cp, sz]),
@@ -476,4 +477,15 @@ def audio_save_wav16(path, audio, sample_rate):
     if not L.mio_tts_audio_save_wav16(path.encode() if path is not None else None,
                                       _ptr(audio, C.c_float) if audio.size else None, audio.size, sample_rate, e,
                                       ERR_SIZE):
+        raise MioTtsError(e.value.decode())
+
+
+def pcm16_static(device, d_audio, offsets, lengths, d_pcm, stream=None):
+    """mio_tts_b200_pcm16_static: WAV16 conversion over DEVICE buffers (raw addresses) with the library's static scratch;
+    allocates nothing.  offsets / lengths are host sequences in samples."""
+    L, e = load_library(), _err_buf()
+    off = np.ascontiguousarray(offsets, dtype=np.int64)
+    ln = np.ascontiguousarray(lengths, dtype=np.int64)
+    if not L.mio_tts_b200_pcm16_static(int(device), C.c_void_p(d_audio), _ptr(off, C.c_int64), _ptr(ln, C.c_int64), off.size,
+                                       C.c_void_p(d_pcm), C.c_void_p(stream), e, ERR_SIZE):
         raise MioTtsError(e.value.decode())
