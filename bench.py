@@ -398,14 +398,14 @@ def aux_configs(m, peaks):
     out["config3_istft"] = {"frames": n_utt * frames, "n_fft": 1920, "hop": 480, "ms": ms, "frames_per_s": n_utt * frames / (ms * 1e-3),
                             "roofline": {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                                          "frac": gbs / peaks["hbm_gbs"]}}
-    # the generic iSTFT kernel (any frame size; the real 44.1 kHz checkpoint's n_fft 392 / hop 98 lands on it)
-    ms392, _ = m.istft_bench(1000, 1000, 392, 98, 5)
-    b392 = (392 + 2) * 4 + 98 * 4
-    out["istft_generic_392_98"] = {"frames": 1000000, "n_fft": 392, "hop": 98, "ms": ms392, "frames_per_s": 1e6 / (ms392 * 1e-3),
-                                   "roofline": {"bound": "hbm", "achieved": 1e6 * b392 / (ms392 * 1e-3) / 1e9,
-                                                "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                                                "frac": 1e6 * b392 / (ms392 * 1e-3) / 1e9 / peaks["hbm_gbs"],
-                                                "bytes_per_frame": b392}}
+    # the frame size of the shipped 44.1 kHz checkpoints (n_fft 392 / hop 98: radix 4x7x7 fast path), and the generic
+    # kernel (any frame size; n_fft 400 / hop 100 has no fast path)
+    for key, nf, hp in (("istft_392_98", 392, 98), ("istft_generic_400_100", 400, 100)):
+        ms_s, _ = m.istft_bench(1000, 1000, nf, hp, 5)
+        b_s = (nf + 2) * 4 + hp * 4
+        out[key] = {"frames": 1000000, "n_fft": nf, "hop": hp, "ms": ms_s, "frames_per_s": 1e6 / (ms_s * 1e-3),
+                    "roofline": {"bound": "hbm", "achieved": 1e6 * b_s / (ms_s * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                                 "frac": 1e6 * b_s / (ms_s * 1e-3) / 1e9 / peaks["hbm_gbs"], "bytes_per_frame": b_s}}
     # codebook gather alone over the config-2 batch (north_star: achieved HBM GB/s of the gather): 25 600 rows x 768 fp32
     # written (79 MB) + the rows read (the 39 MB table is L2-resident after the first pass)
     m.prepare(U.config2_workload(0, BATCH, N_CODES), [U.speaker_embedding()] * BATCH)   # (the iSTFT legs reused the batch tables)

@@ -1,4 +1,4 @@
-// Fast path of the fused iSTFT for the common frame sizes (n_fft = 4*hop, n_fft/2 in {960, 1024, 640}).
+// Fast path of the fused iSTFT for the common frame sizes (n_fft = 4*hop, n_fft/2 in {960, 1024, 640, 196}).
 //
 // Same math and summation order as istft.cu (see its header for the derivation and the reference lines,
 // /root/reference/src/mio-tts-lib.cpp:518-756), restructured for throughput:
@@ -75,6 +75,22 @@ template <int R> __device__ __forceinline__ void dft_small(float2 (&v)[R]) {   /
         const float2 m = fma2(bc(-0.5f), s, v[0]);
         const float2 id = mul2(bc(s3), cmul_i(d));
         v[0] = cadd(v[0], s); v[1] = cadd(m, id); v[2] = csub(m, id);
+    } else if constexpr (R == 7) {
+        // X[m] = v0 + sum_k cos(2 pi m k / 7) (v[k] + v[7-k]) + i sum_k sin(2 pi m k / 7) (v[k] - v[7-k]),  k = 1..3
+        const float c1 = 0.62348980185873353053f, c2 = -0.22252093395631440429f, c3 = -0.90096886790241912624f;
+        const float s1 = 0.78183148246802980871f, s2 = 0.97492791218182360702f, s3 = 0.43388373911755812048f;
+        const float2 a1 = cadd(v[1], v[6]), a2 = cadd(v[2], v[5]), a3 = cadd(v[3], v[4]);
+        const float2 b1 = csub(v[1], v[6]), b2 = csub(v[2], v[5]), b3 = csub(v[3], v[4]);
+        const float2 m1 = fma2(bc(c3), a3, fma2(bc(c2), a2, fma2(bc(c1), a1, v[0])));
+        const float2 m2 = fma2(bc(c1), a3, fma2(bc(c3), a2, fma2(bc(c2), a1, v[0])));
+        const float2 m3 = fma2(bc(c2), a3, fma2(bc(c1), a2, fma2(bc(c3), a1, v[0])));
+        const float2 n1 = cmul_i(fma2(bc(s3), b3, fma2(bc(s2), b2, mul2(bc(s1), b1))));
+        const float2 n2 = cmul_i(fma2(bc(-s1), b3, fma2(bc(-s3), b2, mul2(bc(s2), b1))));
+        const float2 n3 = cmul_i(fma2(bc(s2), b3, fma2(bc(-s1), b2, mul2(bc(s3), b1))));
+        v[0] = cadd(v[0], cadd(a1, cadd(a2, a3)));
+        v[1] = cadd(m1, n1); v[6] = csub(m1, n1);
+        v[2] = cadd(m2, n2); v[5] = csub(m2, n2);
+        v[3] = cadd(m3, n3); v[4] = csub(m3, n3);
     } else {
         static_assert(R == 5, "radix");
         const float c1 = 0.30901699437494742410f, c2 = -0.80901699437494742410f;
@@ -138,7 +154,7 @@ template <int R1, int R2> __device__ __forceinline__ void dft_ct(float2 (&v)[R1 
 }
 
 template <int R> __device__ __forceinline__ void dft_any(float2 (&v)[R]) {
-    if constexpr (R <= 5) dft_small<R>(v);
+    if constexpr (R <= 5 || R == 7) dft_small<R>(v);
     else if constexpr (R == 16) dft_ct<4, 4>(v);
     else if constexpr (R == 15) dft_ct<3, 5>(v);
     else { static_assert(R == 10, "radix"); dft_ct<2, 5>(v); }
@@ -242,8 +258,8 @@ __global__ void __launch_bounds__(FW * 32, 16 / FW) istft_fast_kernel(const fast
     MIO_PDL_PROLOGUE();
     constexpr int FTHREADS = FW * 32;
     constexpr int M = N / 2, H = N / 4, CARRY = N - H, SPAN = FW * H, MP = padded_len<M>::value;
-    constexpr int TWL = tw_table_len<M, 1, RADIX...>::value;
-    static_assert(H % 4 == 0 && MP % 2 == 0 && TWL % 2 == 0, "16-byte rows");
+    constexpr int TWL = (tw_table_len<M, 1, RADIX...>::value + 1) & ~1;
+    static_assert(H % 2 == 0 && MP % 2 == 0 && TWL % 2 == 0, "8-byte rows (16-byte when the hop is a multiple of 4)");
     extern __shared__ __align__(16) uint8_t smem[];
     float2 * s_buf = reinterpret_cast<float2 *>(smem);                  // [FW][MP]
     float2 * s_tw = s_buf + (size_t) FW * MP;                           // per-pass twiddles (TWL float2 units, even)
@@ -336,6 +352,59 @@ __global__ void __launch_bounds__(FW * 32, 16 / FW) istft_fast_kernel(const fast
         float * carry_out = s_carry + (cur ^ 1) * CARRY;
         // A thread keeps one 4-sample column r of the hop and walks the hops q = grp, grp + GROUPS, ...: its window
         // values hs[r + d*H] and its envelope are the same for every hop, so they are loaded once per round.
+        if constexpr (H % 4 != 0) {
+            // hop not a multiple of 4 (n_fft 392 / hop 98 of the 44.1 kHz checkpoints): two-sample columns; the crop
+            // (n_fft - hop) / 2 is odd there, so emitted samples are bounds-checked and stored one by one
+            constexpr int H2 = H / 2, GROUPS = FTHREADS / H2;
+            const int grp = threadIdx.x / H2, r = (threadIdx.x - grp * H2) * 2;
+            if (grp < GROUPS) {
+                float2 hsd[4];
+#pragma unroll
+                for (int d = 0; d < 4; ++d) hsd[d] = *reinterpret_cast<const float2 *>(s_hs + r + d * H);
+                const float2 ie = *reinterpret_cast<const float2 *>(s_env + r);
+                for (int q = grp; q < FW + 3; q += GROUPS) {
+                    const int x = q * H + r;
+                    float2 a0 = make_float2(0.0f, 0.0f);
+                    if (q < 3) a0 = *reinterpret_cast<const float2 *>(carry_in + x);
+#pragma unroll
+                    for (int d = 3; d >= 0; --d) {
+                        const int w = q - d;
+                        if (w >= 0 && w < n_valid) {
+                            const float2 z = *reinterpret_cast<const float2 *>(reinterpret_cast<const float *>(s_buf + (size_t) w * MP) + r + d * H);
+                            const float xm = s_xm[w];
+                            a0 = fma2(cadd(z, make_float2(xm, -xm)), hsd[d], a0);   // r + d*H is even
+                        }
+                    }
+                    if (q >= FW) { *reinterpret_cast<float2 *>(carry_out + (x - SPAN)) = a0; continue; }
+                    const int ri = rel0 + x;
+                    if (ri + 1 < ri_lo || ri >= ri_hi) continue;
+                    const int fi = (int) lr0 + q;
+                    float y[2];
+                    if (fi >= 3 && fi <= S - 1) {
+                        const float2 y0 = mul2(a0, ie);
+                        y[0] = y0.x; y[1] = y0.y;
+                    } else {
+                        const int e_lo = fi - 3 > 0 ? fi - 3 : 0;
+                        const int e_hi = fi < S - 1 ? fi : S - 1;
+                        float e[2] = {0.0f, 0.0f};
+                        for (int f = e_lo; f <= e_hi; ++f) {
+#pragma unroll
+                            for (int c = 0; c < 2; ++c) { const float hv = P.hann[r + c + (fi - f) * H]; e[c] += hv * hv; }
+                        }
+                        y[0] = e[0] > 1e-12f ? a0.x / e[0] : a0.x;
+                        y[1] = e[1] > 1e-12f ? a0.y / e[1] : a0.y;
+                    }
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) {
+                        if (ri + c >= ri_lo && ri + c < ri_hi) {
+                            out_base[ri + c] = y[c];
+                            const float av = fabsf(y[c]);
+                            peak = fmaxf(peak, av <= 3.402823466e38f ? av : 0.0f);
+                        }
+                    }
+                }
+            }
+        } else {
         constexpr int H4 = H / 4, GROUPS = FTHREADS / H4;
         const int grp = threadIdx.x / H4, r = (threadIdx.x - grp * H4) * 4;
         if (grp < GROUPS) {
@@ -386,6 +455,7 @@ __global__ void __launch_bounds__(FW * 32, 16 / FW) istft_fast_kernel(const fast
                 for (int c = 0; c < 4; ++c) peak = fmaxf(peak, av[c] <= 3.402823466e38f ? av[c] : 0.0f);
             }
         }
+        }
         cur ^= 1;
         __syncthreads();
     }
@@ -401,7 +471,7 @@ template <int FW, int N, int... RADIX>
 void launch_fast_t(fast_params P, const int * h_frames, int n_utt, int max_frames, cudaStream_t st) {
     constexpr int FTHREADS = FW * 32;
     constexpr int M = N / 2, H = N / 4, MP = padded_len<M>::value;
-    constexpr int TWL = tw_table_len<M, 1, RADIX...>::value;
+    constexpr int TWL = (tw_table_len<M, 1, RADIX...>::value + 1) & ~1;
     const size_t smem = (size_t) FW * MP * 8 + (size_t) TWL * 8 + (size_t) (M / 2 + 2) * 8 + (size_t) N * 4 + (size_t) H * 4 +
                         (size_t) 2 * (N - H) * 4 + FW * 8 + 64;
     static bool configured[64] = {false};
@@ -442,7 +512,7 @@ bool launch_istft_fast(const istft_plan & p, const float * spec, int pitch, cons
                        const long long * audio_off, float * audio, unsigned int * peak_bits, int n_utt, int max_frames,
                        cudaStream_t st) {
     if (p.hop * 4 != p.n_fft) return false;
-    if (p.n_fft != 1920 && p.n_fft != 2048 && p.n_fft != 1280) return false;
+    if (p.n_fft != 1920 && p.n_fft != 2048 && p.n_fft != 1280 && p.n_fft != 392) return false;
     fast_params P;
     P.n_freq = p.n_fft / 2 + 1;
     P.pad = (p.n_fft - p.hop) / 2;
@@ -456,6 +526,7 @@ bool launch_istft_fast(const istft_plan & p, const float * spec, int pitch, cons
     switch (p.n_fft) {                                                                                    \
         case 1920: launch_fast_t<FWV, 1920, 16, 15, 4>(P, nullptr, n_utt, max_frames, st); break;          \
         case 2048: launch_fast_t<FWV, 2048, 16, 16, 4>(P, nullptr, n_utt, max_frames, st); break;          \
+        case 392: launch_fast_t<FWV, 392, 4, 7, 7>(P, nullptr, n_utt, max_frames, st); break;              \
         default: launch_fast_t<FWV, 1280, 16, 10, 4>(P, nullptr, n_utt, max_frames, st); break;           \
     }
     if (fw == 16) { MIO_ISTFT_CASE(16) } else if (fw == 4) { MIO_ISTFT_CASE(4) } else { MIO_ISTFT_CASE(8) }

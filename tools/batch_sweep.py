@@ -21,13 +21,14 @@ def main():
     ap.add_argument("--codes", type=int, default=400)
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--gemm-log", action="store_true")
+    ap.add_argument("--preset", default="default", help="synthetic-weight preset (tools/make_synth_gguf.py), e.g. upsampler")
     args = ap.parse_args()
     if args.gemm_log:
         os.environ["MIO_TTS_B200_GEMM_LOG"] = "1"
     from mio_tts_cpp_b200 import MioTTS
     from mio_tts_cpp_b200 import benchutil as U
 
-    m = MioTTS(U.synth_gguf("default"))
+    m = MioTTS(U.synth_gguf(args.preset))
     emb = U.speaker_embedding()
     sr = m.sample_rate()
     for b in [int(x) for x in args.batches.split(",")]:
@@ -38,7 +39,7 @@ def main():
         ms = m.run_resident(args.iters)
         secs = m.resident_samples() / sr
         p = m.profile_resident()
-        print(json.dumps({"batch": b, "codes": args.codes, "ms_per_step": ms, "audio_s_per_s": secs / (ms * 1e-3),
+        print(json.dumps({"preset": args.preset, "batch": b, "codes": args.codes, "ms_per_step": ms, "audio_s_per_s": secs / (ms * 1e-3),
                           "stages": {k: round(v, 3) for k, v in p.items() if k.endswith("_ms")},
                           "gemm_tflops": p["gemm_flops"] / (p["gemm_ms"] * 1e-3) / 1e12}), flush=True)
     m.free()
