@@ -113,7 +113,9 @@ struct gemm_args {
     //   tap_shift 1 (taps 0,1 = the two frames of pair row r, tap 2 = first frame of pair row r+1).  grouped conv:
     //   a_col0 = first input channel of the group, tap_row0 = -padding.
     int tap_row0, tap_shift, a_col0;
-    int act;                 // activation after bias: 0 none, 1 GELU (ggml: tanh form through fp16), 2 tanh
+    int act;                 // activation after bias: 0 none, 1 GELU (ggml: tanh form through fp16), 2 tanh,
+                             // 3 SnakeBeta x + snake_ib[n] * sin^2(snake_a[n] * x) (EPI_STORE32 without gate / residual, EPI_STORE16)
+    const float * snake_a; const float * snake_ib;   // per output column, padded to a multiple of 32 columns
     int dtype;               // op16 of A and W
     int out_dtype;           // op16 of a 16-bit output
     int epilogue;
@@ -162,6 +164,8 @@ void launch_layernorm(const float * x, int rows, int dim, float eps, const float
                       const float * cond, int cond_ld, int shift_off, int scale_off, const int * row_utt,
                       void * out16, int out_dtype, float * out32, cudaStream_t st);
 void launch_cast16(const float * x, void * out16, int out_dtype, size_t n, cudaStream_t st);
+// the same with rows that carry no data (row_utt < 0) written as zeros
+void launch_cast16_rows(const float * x, void * out16, int out_dtype, int rows, int cols, const int * row_utt, cudaStream_t st);
 void launch_gn_stats(const float * x, int dim, int groups, const row_tile * tiles, int n_tiles, double * stats,
                      cudaStream_t st);
 // (sum, sumsq) -> (mean, rstd) per (utterance, group), then normalise + affine + SiLU -> 16-bit conv operand; gap rows

@@ -283,7 +283,23 @@ void engine::prepare(const int32_t * const * codes, const size_t * n_codes, cons
                 if (o <= 0) throw std::runtime_error("MioCodec decode failed: wave upsampler crop became non-positive");
                 l = (int) o;
             }
-            build_layout(ups_[i], cur, 1);
+            if (s.poly) {
+                // polyphase stage: the output is the GEMM's [rows, factor*cout] result seen as [rows*factor, cout], so the
+                // next layout is the input layout scaled by the factor (utterance u at factor*row0[u]; gaps stay >= 1 row)
+                const seq_layout & in = i == 0 ? frm_ : ups_[i - 1];
+                seq_layout & L = ups_[i];
+                L = seq_layout();
+                L.n_utt = in.n_utt; L.gap = in.gap * s.factor; L.len = cur; L.row0.resize(cur.size());
+                for (size_t u = 0; u < cur.size(); ++u) {
+                    if (cur[u] != in.len[u] * s.factor) throw std::runtime_error("MioCodec decode failed: polyphase upsampler length mismatch");
+                    L.row0[u] = in.row0[u] * s.factor;
+                    L.max_len = std::max(L.max_len, cur[u]);
+                    L.valid += cur[u];
+                }
+                L.rows = in.rows * s.factor;
+            } else {
+                build_layout(ups_[i], cur, 1);
+            }
         }
     }
     spec_ = ups_.empty() ? &frm_ : &ups_.back();
@@ -332,6 +348,7 @@ void engine::prepare(const int32_t * const * codes, const size_t * n_codes, cons
     size_t f32_elems = std::max(RF * dd, RT * 2 * dd);
     size_t a16_elems = std::max(RT * pd, RF * dd);
     int gmax = 1;
+    size_t up_head16 = 0;       // the fused out_proj + SnakeBeta writes the head's 16-bit operand into ff16_
     for (auto & rb : mdl->prior) gmax = std::max(gmax, rb.groups);
     for (auto & rb : mdl->post) gmax = std::max(gmax, rb.groups);
     {
@@ -346,7 +363,7 @@ void engine::prepare(const int32_t * const * codes, const size_t * n_codes, cons
             gmax = std::max(gmax, s.rb.groups);
             rows_in = rows_out;
         }
-        if (!mdl->ups.empty()) f32_elems = std::max(f32_elems, rows_in * (size_t) mdl->head_in);
+        if (!mdl->ups.empty()) { f32_elems = std::max(f32_elems, rows_in * (size_t) mdl->head_in); up_head16 = rows_in * (size_t) mdl->head_in; }
         a16_elems = std::max(a16_elems, rows_in * (size_t) mdl->head_in);
     }
     const size_t RS = pad_rows(spec_->rows);
@@ -361,7 +378,7 @@ void engine::prepare(const int32_t * const * codes, const size_t * n_codes, cons
     ensure(act16_, a16_elems * 2);
     ensure(qkv16_, std::max(RT * 3 * pd, RF * 3 * dd) * 2);
     ensure(att16_, std::max(RT * pd, RF * dd) * 2);
-    ensure(ff16_, std::max(std::max(RT * hp.prenet_ff, RF * hp.decoder_ff), RT * dd) * 2);
+    ensure(ff16_, std::max(std::max(std::max(RT * hp.prenet_ff, RF * hp.decoder_ff), RT * dd), up_head16) * 2);
     ensure(cond_, std::max<size_t>(16, batch * (size_t) mdl->cond_total * 4));
     ensure(gn_stats_, std::max<size_t>(16, (size_t) n_gn_slots_ * batch * gmax * 2 * sizeof(double)));
     ensure(spec_buf_, RS * spec_pitch_ * 4);
@@ -432,6 +449,7 @@ void engine::gemm(const dbuf & a, const dev_linear & w, int M, int epilogue, voi
     g.row_utt = lay ? lay->d_row_utt : nullptr;
     g.row_pos = lay ? lay->d_row_pos : nullptr;
     g.gn_stats = gn_stats; g.gn_groups = gn_groups;
+    if (snake_a_ != nullptr) { g.act = 3; g.snake_a = snake_a_; g.snake_ib = snake_ib_; }
     if (epilogue == EPI_ROPE16) {
         const int dim = w.N / 3;
         g.rope = rope; g.rope_cols = 2 * dim; g.head_dim = dim / heads;   // (the 1/sqrt(head_dim) q scale lives in Wq)
@@ -706,14 +724,24 @@ void engine::run_direct(bool with_istft, stage_times * prof, int stop_stage) {
     if (stop(5, fx, dd, 0, 0, &frm_)) return;
     const seq_layout * cur = &frm_;
     int cur_c = dd;
+    const dbuf * head_in16 = &act16_;
     for (size_t i = 0; i < mdl->ups.size(); ++i) {
         const upstage & s = mdl->ups[i];
         const seq_layout & nxt = ups_[i];
         flip();
-        launch_cast16(fx, act16_.p, mdl->conv_dtype, (size_t) cur->rows * cur_c, st_);
-        gemm(act16_, s.up, cur->rows, EPI_STORE32, ft, s.ksize * s.cout, 0, nullptr, nullptr, 0, nullptr, cur);
-        launch_convt_fold_snake(ft, s.ksize * s.cout, cur->d_row0, cur->d_len, fy, nxt.rows, s.cout, s.ksize, s.factor,
-                                s.pad, s.up_bias, s.snake_a, s.snake_inv_b, nxt.d_row_utt, nxt.d_row_pos, st_);
+        if (s.poly) {
+            // one implicit GEMM: 3 row-shifted taps of the input (gap rows zeroed: the taps read them as padding),
+            // bias + SnakeBeta in the epilogue, output rows written straight into the upsampled layout
+            launch_cast16_rows(fx, act16_.p, mdl->conv_dtype, cur->rows, cur_c, cur->d_row_utt, st_);
+            snake_a_ = s.poly_snake_a; snake_ib_ = s.poly_snake_inv_b;
+            gemm(act16_, s.up_poly, cur->rows, EPI_STORE32, fy, s.factor * s.cout, 0, s.poly_bias, nullptr, 0, nullptr, cur);
+            snake_a_ = snake_ib_ = nullptr;
+        } else {
+            launch_cast16(fx, act16_.p, mdl->conv_dtype, (size_t) cur->rows * cur_c, st_);
+            gemm(act16_, s.up, cur->rows, EPI_STORE32, ft, s.ksize * s.cout, 0, nullptr, nullptr, 0, nullptr, cur);
+            launch_convt_fold_snake(ft, s.ksize * s.cout, cur->d_row0, cur->d_len, fy, nxt.rows, s.cout, s.ksize, s.factor,
+                                    s.pad, s.up_bias, s.snake_a, s.snake_inv_b, nxt.d_row_utt, nxt.d_row_pos, st_);
+        }
         std::swap(fx, fy);
         run_resblock(fx, fy, nxt, s.rb, gn_slot, false, false);
         cur = &nxt;
@@ -722,16 +750,26 @@ void engine::run_direct(bool with_istft, stage_times * prof, int stop_stage) {
     if (!mdl->ups.empty()) {
         flip();
         launch_cast16(fx, act16_.p, ldt, (size_t) cur->rows * cur_c, st_);
-        gemm(act16_, mdl->up_out_proj, cur->rows, EPI_STORE32, ft, mdl->head_in, 0, mdl->up_out_proj.bias, nullptr, 0,
-             nullptr, cur);
-        launch_snake(ft, cur->rows, mdl->head_in, mdl->out_snake_a, mdl->out_snake_inv_b, st_);
-        flip();
-        launch_cast16(ft, act16_.p, ldt, (size_t) cur->rows * mdl->head_in, st_);
+        static const bool fuse_snake = [] { const char * e = std::getenv("MIO_TTS_B200_CONVT_POLY"); return !(e && e[0] == '0'); }();
+        if (fuse_snake) {
+            // out_proj + bias + SnakeBeta -> the head's 16-bit operand in one epilogue (no fp32 round trip, no snake / cast passes)
+            snake_a_ = mdl->out_snake_a_pad; snake_ib_ = mdl->out_snake_inv_b_pad;
+            gemm(act16_, mdl->up_out_proj, cur->rows, EPI_STORE16, ff16_.p, mdl->head_in, ldt, mdl->up_out_proj.bias, nullptr, 0,
+                 nullptr, cur);
+            snake_a_ = snake_ib_ = nullptr;
+            head_in16 = &ff16_;
+        } else {
+            gemm(act16_, mdl->up_out_proj, cur->rows, EPI_STORE32, ft, mdl->head_in, 0, mdl->up_out_proj.bias, nullptr, 0,
+                 nullptr, cur);
+            launch_snake(ft, cur->rows, mdl->head_in, mdl->out_snake_a, mdl->out_snake_inv_b, st_);
+            flip();
+            launch_cast16(ft, act16_.p, ldt, (size_t) cur->rows * mdl->head_in, st_);
+        }
     } else {
         flip();
         launch_cast16(fx, act16_.p, ldt, (size_t) cur->rows * cur_c, st_);
     }
-    gemm(act16_, mdl->head, cur->rows, EPI_STORE32, spec_buf_.p, spec_pitch_, 0, mdl->head.bias, nullptr, 0, nullptr, cur);
+    gemm(*head_in16, mdl->head, cur->rows, EPI_STORE32, spec_buf_.p, spec_pitch_, 0, mdl->head.bias, nullptr, 0, nullptr, cur);
     mark(4);
 
     if (with_istft) {

@@ -103,6 +103,7 @@ private:
     std::vector<long long> audio_off_, audio_len_;
     long long audio_total_ = 0;
     int n_gn_slots_ = 0, gn_groups_max_ = 1;
+    const float * snake_a_ = nullptr, * snake_ib_ = nullptr;   // SnakeBeta vectors of the next gemm() call (act 3)
     size_t h2d_bytes_ = 0;
     // metadata blob (pinned host + device)
     std::vector<uint8_t> blob_;

@@ -239,13 +239,25 @@ __device__ __forceinline__ float act_apply(float x, int act) {
     return x;
 }
 
+// SnakeBeta (/root/reference/src/miocodec-decoder.cpp:1332-1343): x + sin^2(alpha x) / beta, the sine on the SFU after a
+// two-constant reduction of the argument to [-pi, pi] (absolute error ~1e-6)
+__device__ __forceinline__ float snake_f(float x, float al, float ib) {
+    const float t = x * al;
+    const float kf = rintf(t * 0.15915494309189535f);
+    float r = fmaf(-kf, 6.2831854820251465f, t);
+    r = fmaf(-kf, -1.7484555e-7f, r);
+    const float sn = __sinf(r);
+    return fmaf(sn * sn, ib, x);
+}
+
 // fp32 box: out = act(acc + bias) * gate + residual, residual read from / result written to the same box slot.
 // BIAS/GATE/RES are compile-time so an absent term costs no issue slots.  The bias / gate values of the chunk (bv, gv)
 // were fetched by the caller one chunk ahead (zeros past N: those columns are clipped by the TMA store).
 // STATS: sq = {sum, sum of squares} of this row's columns 0-15 and 16-31 of the chunk (final values, residual included).
-template <bool BIAS, bool GATE, bool RES, bool STATS = false>
+// SNAKE: act 3; gv holds the chunk's alpha values (fetched like a gate), the 1/beta values are read here.
+template <bool BIAS, bool GATE, bool RES, bool STATS = false, bool SNAKE = false>
 __device__ __forceinline__ void chunk_store32(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, int lane,
-                                              const float4 (&bv)[8], const float4 (&gv)[8], float (&sq)[4]) {
+                                              const float4 (&bv)[8], const float4 (&gv)[8], float (&sq)[4], int n = 0) {
     const uint32_t row = buf + lane * 128;
     const uint32_t sw = (uint32_t) (lane & 7) << 4;
     if (STATS) { sq[0] = sq[1] = sq[2] = sq[3] = 0.0f; }
@@ -255,7 +267,11 @@ __device__ __forceinline__ void chunk_store32(const gemm_args & a, const uint32_
         float4 o = make_float4(__uint_as_float(raw[4 * j]), __uint_as_float(raw[4 * j + 1]), __uint_as_float(raw[4 * j + 2]),
                                __uint_as_float(raw[4 * j + 3]));
         if (BIAS) { o.x += bv[j].x; o.y += bv[j].y; o.z += bv[j].z; o.w += bv[j].w; }
-        if (a.act != 0) {   // warp-uniform
+        if constexpr (SNAKE) {
+            const float4 ib = __ldg(reinterpret_cast<const float4 *>(a.snake_ib + n) + j);
+            o.x = snake_f(o.x, gv[j].x, ib.x); o.y = snake_f(o.y, gv[j].y, ib.y);
+            o.z = snake_f(o.z, gv[j].z, ib.z); o.w = snake_f(o.w, gv[j].w, ib.w);
+        } else if (a.act != 0) {   // warp-uniform
             o.x = act_apply(o.x, a.act); o.y = act_apply(o.y, a.act); o.z = act_apply(o.z, a.act); o.w = act_apply(o.w, a.act);
         }
         if (GATE) { o.x *= gv[j].x; o.y *= gv[j].y; o.z *= gv[j].z; o.w *= gv[j].w; }
@@ -274,7 +290,11 @@ __device__ __forceinline__ void chunk_store32(const gemm_args & a, const uint32_
 // warp-uniform dispatch to the term combinations in use; has_res: the residual sits in the box and is added here
 // (false in reduce-add mode, where the box carries the new term alone)
 __device__ __forceinline__ void chunk_store32_any(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, int lane,
-                                                  const float4 (&bv)[8], const float4 (&gv)[8], bool has_res, float (&sq)[4]) {
+                                                  const float4 (&bv)[8], const float4 (&gv)[8], bool has_res, float (&sq)[4], int n) {
+    if (a.act == 3) {   // polyphase transposed convolution of the wave upsampler: bias, SnakeBeta, plain store
+        chunk_store32<true, false, false, false, true>(a, raw, buf, lane, bv, gv, sq, n);
+        return;
+    }
     if (a.gn_stats) {   // the k=3 convolutions of the resnet blocks: bias, no gate; conv2 with the residual in the box
         if (has_res) chunk_store32<true, false, true, true>(a, raw, buf, lane, bv, gv, sq);
         else chunk_store32<true, false, false, true>(a, raw, buf, lane, bv, gv, sq);
@@ -323,7 +343,17 @@ __device__ __forceinline__ void chunk_store16(const gemm_args & a, const uint32_
                 x[4 * h] += b.x; x[4 * h + 1] += b.y; x[4 * h + 2] += b.z; x[4 * h + 3] += b.w;
             }
         }
-        if (!ROPE && a.act != 0) {   // warp-uniform
+        if (!ROPE && a.act == 3) {   // warp-uniform
+            if (n + 8 * j < a.N) {
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const float4 al = __ldg(reinterpret_cast<const float4 *>(a.snake_a + n) + 2 * j + h);
+                    const float4 ib = __ldg(reinterpret_cast<const float4 *>(a.snake_ib + n) + 2 * j + h);
+                    x[4 * h] = snake_f(x[4 * h], al.x, ib.x); x[4 * h + 1] = snake_f(x[4 * h + 1], al.y, ib.y);
+                    x[4 * h + 2] = snake_f(x[4 * h + 2], al.z, ib.z); x[4 * h + 3] = snake_f(x[4 * h + 3], al.w, ib.w);
+                }
+            }
+        } else if (!ROPE && a.act != 0) {   // warp-uniform
 #pragma unroll
             for (int e = 0; e < 8; ++e) x[e] = act_apply(x[e], a.act);
         }
@@ -568,6 +598,7 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
             int utt_row = 0;
             if constexpr (EPI == EPI_STORE32) {
                 if (a.gate) gate_row = a.gate + (size_t) max(utt_next, 0) * a.gate_ld;
+                if (a.act == 3) gate_row = a.snake_a;          // SnakeBeta alpha per column, fetched like a gate
                 utt_row = utt_next;
                 utt_next = utt_of(t + n_units);
             } else if constexpr (EPI == EPI_ROPE16) {
@@ -666,7 +697,7 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
                     else { if (lane == 0) bulk_wait_read<EPI_NBUF - 1>(); __syncwarp(); }
                     tmem_ld_wait();
                     float sq[4];
-                    chunk_store32_any(a, raw, buf, lane, bv, gv, has_res, sq);
+                    chunk_store32_any(a, raw, buf, lane, bv, gv, has_res, sq, n);
                     bg_fetch(c + EW);
                     if (a.gn_stats != nullptr) {
                         // GroupNorm statistics of the consumer: this row's two 16-column halves of the chunk
@@ -871,6 +902,9 @@ void gemm_launch(const gemm_args & a, int num_sms, cudaStream_t st) {
     if (a.M <= 0 || a.N <= 0 || a.K <= 0) return;
     if (a.epilogue == EPI_ROPE16 && (a.head_dim % 32) != 0) throw cuda_error("gemm: rope epilogue needs head_dim % 32 == 0");
     if (a.res != nullptr && a.res != a.out) throw cuda_error("gemm: the residual must be the (in-place) output");
+    if (a.act == 3 && (a.snake_a == nullptr || a.snake_ib == nullptr || a.bias == nullptr || a.gate != nullptr || a.res != nullptr ||
+                       a.gn_stats != nullptr || (a.epilogue != EPI_STORE32 && a.epilogue != EPI_STORE16)))
+        throw cuda_error("gemm: the SnakeBeta epilogue needs bias and the per-column alpha / 1/beta vectors, and no gate, residual or statistics");
     static const bool use_red = [] { const char * e = std::getenv("MIO_TTS_B200_GEMM_RED"); return !(e && e[0] == '0'); }();
     static int ew = -1, ncta = -1;
     if (ew < 0) {   // epilogue warps per TMEM lane quadrant

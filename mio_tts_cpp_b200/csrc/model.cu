@@ -173,9 +173,43 @@ struct loader {
                 for (int kk = 0; kk < ksize; ++kk)
                     r[((size_t) kk * cout + co) * cin + ci] = w[((size_t) ci * cout + co) * ksize + kk];
         make_linear(L, r, ksize * cout, cin, 1, dtype, nullptr);
+        w_last_convt = std::move(w);
+        return true;
+    }
+    std::vector<float> w_last_convt;   // [cin][cout][k] of the transposed convolution loaded last (polyphase repack)
+
+    // Polyphase weights of a transposed convolution (model.h, upstage): out[t*f + p] = sum_j x[t + (p + pad - j)/f] W[:, :, j]
+    // over the taps j with (p + pad - j) divisible by f.  Returns false when a tap falls outside rows t-1 .. t+1 or the
+    // output is not exactly f rows per input row.
+    bool convt_poly(upstage & st, const std::vector<float> & bias, const std::vector<float> & al, const std::vector<float> & ib,
+                    int dtype) {
+        const int f = st.factor, k = st.ksize, pad = st.pad, cin = st.cin, cout = st.cout;
+        if (k - 2 * pad != f || (cin % 64) != 0 || ((f * cout) % 8) != 0) return false;
+        for (int p = 0; p < f; ++p)
+            for (int j = 0; j < k; ++j)
+                if ((p + pad - j) % f == 0 && std::abs((p + pad - j) / f) > 1) return false;
+        const int N = f * cout;
+        std::vector<float> r((size_t) N * 3 * cin, 0.0f);
+        for (int p = 0; p < f; ++p)
+            for (int j = 0; j < k; ++j) {
+                if ((p + pad - j) % f != 0) continue;
+                const int tap = (p + pad - j) / f + 1;          // GEMM tap 0 / 1 / 2 reads input row t-1 / t / t+1
+                for (int co = 0; co < cout; ++co)
+                    for (int ci = 0; ci < cin; ++ci)
+                        r[((size_t) (p * cout + co) * 3 + tap) * cin + ci] = w_last_convt[((size_t) ci * cout + co) * k + j];
+            }
+        make_linear(st.up_poly, r, N, cin, 3, dtype, nullptr);
+        const size_t np = ((size_t) N + 31) / 32 * 32;
+        std::vector<float> b(np, 0.0f), a(np, 0.0f), i2(np, 0.0f);
+        for (int n = 0; n < N; ++n) { b[n] = bias[n % cout]; a[n] = al[n % cout]; i2[n] = ib[n % cout]; }
+        st.poly_bias = m.upload_f32(b.data(), b.size());
+        st.poly_snake_a = m.upload_f32(a.data(), a.size());
+        st.poly_snake_inv_b = m.upload_f32(i2.data(), i2.size());
+        st.poly = true;
         return true;
     }
 
+    std::vector<float> snake_al, snake_ib;   // host copies of the vectors loaded last (exp(alpha), 1 / (exp(beta) + 1e-9))
     bool snake(const std::string & prefix, int c, float *& a, float *& inv_b) {
         std::vector<float> al, be;
         if (!get(prefix + ".alpha", al, (size_t) c) || !get(prefix + ".beta", be, (size_t) c)) return false;
@@ -183,6 +217,7 @@ struct loader {
         for (int i = 0; i < c; ++i) { al[i] = expf(al[i]); be[i] = 1.0f / (expf(be[i]) + 1e-9f); }
         a = m.upload_f32(al.data(), al.size());
         inv_b = m.upload_f32(be.data(), be.size());
+        snake_al = al; snake_ib = be;
         return true;
     }
 };
@@ -365,6 +400,8 @@ bool model::load(const std::string & path, int dev, std::string & err) {
             if (st.cout % 4) { err = "wave upsampler channel counts must be multiples of 4"; return false; }
             st.up_bias = upload_f32(b.data(), b.size());
             if (!L.snake("wave_upsampler.snake." + si, st.cout, st.snake_a, st.snake_inv_b)) return false;
+            static const bool poly_env = [] { const char * e = std::getenv("MIO_TTS_B200_CONVT_POLY"); return !(e && e[0] == '0'); }();
+            if (poly_env) L.convt_poly(st, b, L.snake_al, L.snake_ib, conv_dtype);
             if (!L.resblock_load("wave_upsampler.resblk." + si, st.cout, st.rb)) return false;
             cin = st.cout;
         }
@@ -375,6 +412,13 @@ bool model::load(const std::string & path, int dev, std::string & err) {
         if (out_dim % 8) { err = "wave upsampler out_proj width must be a multiple of 8"; return false; }
         if (!L.linear("wave_upsampler.out_proj.weight", "wave_upsampler.out_proj.bias", out_dim, cin, up_out_proj)) return false;
         if (!L.snake("wave_upsampler.out_snake", out_dim, out_snake_a, out_snake_inv_b)) return false;
+        {
+            std::vector<float> a2(((size_t) out_dim + 31) / 32 * 32, 0.0f), i2(a2.size(), 0.0f);
+            std::copy(L.snake_al.begin(), L.snake_al.end(), a2.begin());
+            std::copy(L.snake_ib.begin(), L.snake_ib.end(), i2.begin());
+            out_snake_a_pad = upload_f32(a2.data(), a2.size());
+            out_snake_inv_b_pad = upload_f32(i2.data(), i2.size());
+        }
         head_in = out_dim;
     }
 

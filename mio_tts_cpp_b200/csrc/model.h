@@ -52,6 +52,13 @@ struct upstage {
     float * snake_a = nullptr, * snake_inv_b = nullptr;
     resblock rb;
     int factor = 1, ksize = 1, pad = 0, cin = 0, cout = 0;
+    // Polyphase form (set when ksize - 2 pad == factor and every tap lands on input row t-1, t or t+1): output row
+    // t*factor + p of an utterance is a 3-tap "same" convolution of the INPUT rows with the kernel taps j = p + pad - s*factor
+    // (s = -1, 0, +1), so the whole stage is ONE implicit GEMM [rows, 3*cin] x [factor*cout, 3*cin]^T whose output, seen as
+    // [rows*factor, cout], is the upsampled sequence -- bias and SnakeBeta in the epilogue, no k*cout intermediate, no fold.
+    bool poly = false;
+    dev_linear up_poly;         // N = factor*cout, K = cin, taps = 3 (zero blocks where a phase has no tap)
+    float * poly_bias = nullptr, * poly_snake_a = nullptr, * poly_snake_inv_b = nullptr;   // [factor*cout], padded to 32
 };
 
 class model {
@@ -72,6 +79,7 @@ public:
     std::vector<resblock> prior, post;
     float * cond_w = nullptr, * cond_b = nullptr; int cond_total = 0, cond_final_off = -1;
     std::vector<upstage> ups; int up_total = 1;
+    float * out_snake_a_pad = nullptr, * out_snake_inv_b_pad = nullptr;   // out_snake vectors padded to 32 columns (GEMM epilogue)
     dev_linear up_out_proj; float * out_snake_a = nullptr, * out_snake_inv_b = nullptr;
     dev_linear head;
     int head_in = 0;              // channels feeding the iSTFT head

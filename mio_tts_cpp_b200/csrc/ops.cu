@@ -257,6 +257,23 @@ __global__ void cast16_kernel(const float * __restrict__ x, void * out16, int ou
     reinterpret_cast<uint2 *>(out16)[i] = o;
 }
 
+// The same cast for an operand whose NEIGHBOUR rows a multi-tap GEMM reads (polyphase transposed convolution): rows
+// that carry no data (row_utt < 0: the gaps between utterances, which in-place residual updates leave dirty) become 0.
+__global__ void cast16_rows_kernel(const float * __restrict__ x, void * out16, int out_dtype, int rows, int c4,
+                                   const int * __restrict__ row_utt, int rev) {
+    MIO_PDL_PROLOGUE();
+    const size_t i = (size_t) MIO_BLOCK_X(rev) * blockDim.x + threadIdx.x;
+    if (i >= (size_t) rows * c4) return;
+    const int row = (int) (i / c4);
+    uint2 o = make_uint2(0u, 0u);
+    if (row_utt[row] >= 0) {
+        const float4 v = reinterpret_cast<const float4 *>(x)[i];
+        o.x = pack16(v.x, v.y, out_dtype);
+        o.y = pack16(v.z, v.w, out_dtype);
+    }
+    reinterpret_cast<uint2 *>(out16)[i] = o;
+}
+
 // ---- GroupNorm phase 1: per (utterance, group) sum and sum of squares over (channels-in-group x ALL frames)
 //      (ggml_group_norm, ggml-cpu/ops.cpp:3955-4028: double accumulators).  One block per <=64-row tile. ----
 template <int VEC>
@@ -545,6 +562,15 @@ void launch_cast16(const float * x, void * out16, int out_dtype, size_t n, cudaS
     if (n == 0) return;
     if (n & 3) throw cuda_error("cast16: element count must be a multiple of 4");
     launch_pdl(cast16_kernel, dim3(blocks_for(n >> 2, 256)), dim3(256), 0, st, x, out16, out_dtype, n >> 2, traversal_reverse());
+    MIO_CUDA(cudaGetLastError());
+    count_launch();
+}
+
+void launch_cast16_rows(const float * x, void * out16, int out_dtype, int rows, int cols, const int * row_utt, cudaStream_t st) {
+    if (rows <= 0) return;
+    if (cols & 3) throw cuda_error("cast16: column count must be a multiple of 4");
+    launch_pdl(cast16_rows_kernel, dim3(blocks_for((size_t) rows * (cols >> 2), 256)), dim3(256), 0, st, x, out16, out_dtype, rows,
+               cols >> 2, row_utt, traversal_reverse());
     MIO_CUDA(cudaGetLastError());
     count_launch();
 }
