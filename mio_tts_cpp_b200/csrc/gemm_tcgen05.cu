@@ -920,6 +920,8 @@ void gemm_launch(const gemm_args & a, int num_sms, cudaStream_t st) {
         if (a.N != 512 || a.taps != 1 || a.res == nullptr || a.ln_a == nullptr || a.ln_b == nullptr || (a.K % BLOCK_K) != 0 ||
             a.gn_stats != nullptr || (a.gate != nullptr && a.row_utt == nullptr))
             throw cuda_error("gemm: the LayerNorm-fused epilogue needs N = 512, one tap, the in-place residual and LN parameters");
+        static const bool ln_pf = [] { const char * e = std::getenv("MIO_TTS_B200_LN_PREFETCH"); return !(e && e[0] == '0'); }();
+        g.ln_prefetch = ln_pf ? 1 : 0;
         launch_ln(g, num_sms, st);
         return;
     }
