@@ -138,6 +138,7 @@ struct gemm_args {
     // (AdaLN: per-utterance scale / shift, ln_plus1 = 1; plain LayerNorm: ln_ld = 0, ln_plus1 = 0); gap rows (utt < 0) -> 0
     CUtensorMap map_out2;                // [rows, N] 16-bit, box 32 x 32, swizzle 64B
     const float * ln_a; const float * ln_b; int ln_ld; float ln_plus1; float ln_eps; int ln_out_dtype;
+    int dbg;                             // timing experiments (MIO_TTS_B200_GEMM_DBG), 0 in production
     int ln_prefetch;                     // L1 prefetch of the item's per-column vectors (MIO_TTS_B200_LN_PREFETCH=0 turns it off): set by gemm_launch
 };
 inline bool gemm_gn_stats_ok(int N, int groups) {

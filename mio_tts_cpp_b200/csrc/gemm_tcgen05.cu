@@ -767,6 +767,7 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
 }
 
 #include "gemm_ln.inc"
+#include "gemm_astat.inc"
 
 typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                     const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
@@ -930,6 +931,7 @@ void gemm_launch(const gemm_args & a, int num_sms, cudaStream_t st) {
         throw cuda_error("gemm: GroupNorm statistics need the fp32-store epilogue with bias, row_utt, no gate, and a supported group width");
     // the statistics are taken over the FINAL values, so the residual has to pass through the SM (no L2 reduce-add)
     g.red_add = (use_red && a.res != nullptr && a.epilogue == EPI_STORE32 && g.gn_stats == nullptr) ? 1 : 0;
+    if (ncta == 2 && astat_applies(g)) { launch_astat(g, num_sms, st); return; }
     if (gemm_block_n(a.N) == 256) {
         if (ncta == 2) { if (ew == 1) launch_bn<256, 1, 2>(g, num_sms, st); else launch_bn<256, 2, 2>(g, num_sms, st); }
         else { if (ew == 1) launch_bn<256, 1, 1>(g, num_sms, st); else launch_bn<256, 2, 1>(g, num_sms, st); }

@@ -416,10 +416,15 @@ def test_gemm_tail_split_is_bit_invariant(gguf_paths, emb):
         "print('HASH', h.hexdigest())\n"
     ) % (ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "tests", "golden", "en_female_emb.npy"), path)
     hashes = {}
-    for mode in ("0", "1", "2", None):
+    # "astat0": the A-stationary SwiGLU GEMM (gemm_astat.inc: A rows resident in shared memory, contiguous item ranges) off,
+    # i.e. the gate/up projections on the generic kernel -- the same K order per element, so the same bits
+    for mode in ("0", "1", "2", None, "astat0"):
         env = dict(os.environ)
         env.pop("MIO_TTS_B200_GEMM_SPLIT", None)
-        if mode is not None:
+        env.pop("MIO_TTS_B200_GEMM_ASTAT", None)
+        if mode == "astat0":
+            env["MIO_TTS_B200_GEMM_ASTAT"] = "0"
+        elif mode is not None:
             env["MIO_TTS_B200_GEMM_SPLIT"] = mode
         out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
         assert out.returncode == 0, out.stderr[-2000:]
