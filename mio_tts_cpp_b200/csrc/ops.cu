@@ -359,8 +359,11 @@ __global__ void gn_apply_kernel(const float * __restrict__ x, int rows, int dim,
 
 // fast path: channels-per-group % 4 == 0 (one statistics lookup per float4) and 256 % (dim/4) == 0, so a thread keeps
 // its channel quad (affine weights in registers) and walks rows; SiLU on the SFU (output is rounded to fp16 anyway)
+// Persistent form: a block owns a CONTIGUOUS run of 8-row chunks (so a thread's rows almost always share one utterance
+// and the double-precision (mean, rstd) tail is derived once per thread, not once per chunk) and the next chunk's loads
+// are in flight while the current one is normalised.
 template <int ROWS_PER_THREAD>
-__global__ void gn_apply_fast_kernel(const float * __restrict__ x, int rows, int dim, int groups,
+__global__ void __launch_bounds__(256, 4) gn_apply_fast_kernel(const float * __restrict__ x, int rows, int dim, int groups,
                                      const double * __restrict__ stats, const int * __restrict__ utt_len, float eps,
                                      const float * __restrict__ w,
                                      const float * __restrict__ b, const int * __restrict__ row_utt, void * out16,
@@ -372,36 +375,50 @@ __global__ void gn_apply_fast_kernel(const float * __restrict__ x, int rows, int
     const int g = (c4 * 4) / (dim / groups);
     const float4 ww = __ldg(reinterpret_cast<const float4 *>(w) + c4);
     const float4 bb = __ldg(reinterpret_cast<const float4 *>(b) + c4);
-    const int row_base = MIO_BLOCK_X(rev) * rpb * ROWS_PER_THREAD + threadIdx.x / c4n;
-    float4 v[ROWS_PER_THREAD];
-    int utt[ROWS_PER_THREAD];
+    const int rows_per_chunk = rpb * ROWS_PER_THREAD;
+    const int n_chunks = (rows + rows_per_chunk - 1) / rows_per_chunk;
+    const int blk = MIO_BLOCK_X(rev);
+    const int c_lo = (int) ((long long) blk * n_chunks / gridDim.x), c_hi = (int) ((long long) (blk + 1) * n_chunks / gridDim.x);
+    float4 v[ROWS_PER_THREAD], vn[ROWS_PER_THREAD];
+    int utt[ROWS_PER_THREAD], uttn[ROWS_PER_THREAD];
+    auto load = [&](int chunk, float4 (&vv)[ROWS_PER_THREAD], int (&uu)[ROWS_PER_THREAD]) {
+        const int row_base = chunk * rows_per_chunk + threadIdx.x / c4n;
 #pragma unroll
-    for (int it = 0; it < ROWS_PER_THREAD; ++it) {
-        const int row = row_base + it * rpb;
-        utt[it] = row < rows ? __ldg(row_utt + row) : -1;
-        if (utt[it] >= 0) v[it] = reinterpret_cast<const float4 *>(x)[(size_t) row * c4n + c4];
-    }
-    int m_utt = -1;                 // the thread's rows almost always share one utterance: (mean, rstd) derived once
-    float2 m = make_float2(0.f, 1.f);
-#pragma unroll
-    for (int it = 0; it < ROWS_PER_THREAD; ++it) {
-        const int row = row_base + it * rpb;
-        if (row >= rows) continue;
-        uint2 o = make_uint2(0u, 0u);
-        if (utt[it] >= 0) {
-            if (utt[it] != m_utt) { m_utt = utt[it]; m = gn_mean_rstd(stats, utt_len, m_utt, groups, g, dim / groups, eps); }
-            float y[4] = {v[it].x, v[it].y, v[it].z, v[it].w};
-            const float wv[4] = {ww.x, ww.y, ww.z, ww.w};
-            const float bv[4] = {bb.x, bb.y, bb.z, bb.w};
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const float t = ((y[k] - m.x) * m.y) * wv[k] + bv[k];
-                y[k] = __fdividef(t, 1.0f + __expf(-t));
-            }
-            o.x = pack16(y[0], y[1], out_dtype);
-            o.y = pack16(y[2], y[3], out_dtype);
+        for (int it = 0; it < ROWS_PER_THREAD; ++it) {
+            const int row = row_base + it * rpb;
+            uu[it] = row < rows ? __ldg(row_utt + row) : -1;
+            if (uu[it] >= 0) vv[it] = reinterpret_cast<const float4 *>(x)[(size_t) row * c4n + c4];
         }
-        reinterpret_cast<uint2 *>(out16)[(size_t) row * c4n + c4] = o;
+    };
+    int m_utt = -1;
+    float2 m = make_float2(0.f, 1.f);
+    if (c_lo < c_hi) load(rev ? c_hi - 1 : c_lo, v, utt);
+    for (int i = 0; i < c_hi - c_lo; ++i) {
+        const int chunk = rev ? c_hi - 1 - i : c_lo + i;
+        if (i + 1 < c_hi - c_lo) load(rev ? chunk - 1 : chunk + 1, vn, uttn);
+        const int row_base = chunk * rows_per_chunk + threadIdx.x / c4n;
+#pragma unroll
+        for (int it = 0; it < ROWS_PER_THREAD; ++it) {
+            const int row = row_base + it * rpb;
+            if (row >= rows) continue;
+            uint2 o = make_uint2(0u, 0u);
+            if (utt[it] >= 0) {
+                if (utt[it] != m_utt) { m_utt = utt[it]; m = gn_mean_rstd(stats, utt_len, m_utt, groups, g, dim / groups, eps); }
+                float y[4] = {v[it].x, v[it].y, v[it].z, v[it].w};
+                const float wv[4] = {ww.x, ww.y, ww.z, ww.w};
+                const float bv[4] = {bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float t = ((y[k] - m.x) * m.y) * wv[k] + bv[k];
+                    y[k] = __fdividef(t, 1.0f + __expf(-t));
+                }
+                o.x = pack16(y[0], y[1], out_dtype);
+                o.y = pack16(y[2], y[3], out_dtype);
+            }
+            reinterpret_cast<uint2 *>(out16)[(size_t) row * c4n + c4] = o;
+        }
+#pragma unroll
+        for (int it = 0; it < ROWS_PER_THREAD; ++it) { v[it] = vn[it]; utt[it] = uttn[it]; }
     }
 }
 
@@ -600,7 +617,13 @@ void launch_gn_apply(const float * x, int rows, int dim, int groups, const doubl
     if ((cpg & 3) == 0 && c4n <= 256 && (256 % c4n) == 0) {
         constexpr int RPT = 4;
         const int rows_per_block = (256 / c4n) * RPT;
-        launch_pdl(gn_apply_fast_kernel<RPT>, dim3(blocks_for((size_t) rows, rows_per_block)), dim3(256), 0, st, 
+        static int n_sm[64] = {0};
+        int dev = 0;
+        MIO_CUDA(cudaGetDevice(&dev));
+        if (n_sm[dev & 63] == 0) MIO_CUDA(cudaDeviceGetAttribute(&n_sm[dev & 63], cudaDevAttrMultiProcessorCount, dev));
+        const unsigned chunks = blocks_for((size_t) rows, rows_per_block);
+        const unsigned grid = std::min<unsigned>(chunks, (unsigned) n_sm[dev & 63] * 4u);     // one resident wave (4 blocks per SM)
+        launch_pdl(gn_apply_fast_kernel<RPT>, dim3(grid), dim3(256), 0, st, 
             x, rows, dim, groups, stats, utt_len, eps, w, b, row_utt, out16, out_dtype, traversal_reverse());
     } else {
         launch_pdl(gn_apply_kernel, dim3(blocks_for((size_t) rows * (dim >> 2), 256)), dim3(256), 0, st, 
