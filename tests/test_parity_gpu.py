@@ -432,6 +432,42 @@ def test_gemm_tail_split_is_bit_invariant(gguf_paths, emb):
     assert len(set(hashes.values())) == 1, hashes
 
 
+@pytest.mark.parametrize("preset", ["upsampler_tiny", "upsampler"])
+def test_polyphase_upsampler_agrees_with_the_fold_path(preset, gguf_paths, emb):
+    """The wave-upsampler stages run as one polyphase implicit GEMM each; MIO_TTS_B200_CONVT_POLY=0 keeps the
+    transposed convolution as GEMM + fold + snake kernels.  Same operands (fp16), different fp32 summation order and a
+    different sine (SFU after range reduction vs sinf): the spectrograms must agree far inside the parity gates, alone and
+    in a ragged batch (the polyphase taps read the gap rows between utterances as padding).  Subprocesses: the switch is
+    read once per process."""
+    path = gguf_paths(preset)[0]
+    out = {}
+    code = (
+        "import sys, numpy as np; sys.path.insert(0, %r)\n"
+        "from mio_tts_cpp_b200 import MioTTS\n"
+        "emb = np.load(%r); rng = np.random.default_rng(9)\n"
+        "m = MioTTS(%r)\n"
+        "codes = [rng.integers(0, 12800, int(t)).astype(np.int32) for t in (1, 2, 37, 64, 5)]\n"
+        "specs = [m.decode_spec(c, emb) for c in codes]\n"
+        "audio = m.synthesize_batch(codes, [emb] * len(codes))[0]\n"
+        "np.savez(sys.argv[1], *specs, *[np.asarray(a) for a in audio])\n"
+    ) % (ROOT, os.path.join(ROOT, "tests", "golden", "en_female_emb.npy"), path)
+    import tempfile
+
+    with tempfile.TemporaryDirectory() as d:
+        for mode in ("0", "1"):
+            env = dict(os.environ, MIO_TTS_B200_CONVT_POLY=mode)
+            f = os.path.join(d, f"o{mode}.npz")
+            r = subprocess.run([sys.executable, "-c", code, f], env=env, capture_output=True, text=True, timeout=600)
+            assert r.returncode == 0, r.stderr[-2000:]
+            z = np.load(f)
+            out[mode] = [z[k] for k in z.files]
+    assert len(out["0"]) == len(out["1"]) == 10
+    for i, (a, b) in enumerate(zip(out["0"], out["1"])):
+        assert a.shape == b.shape
+        db = snr_db(b, a)
+        assert db >= (60.0 if i < 5 else 50.0), (preset, i, db)     # spectrograms / waveforms; measured > 70 / > 60 dB
+
+
 def test_pipelined_halves_match_single_calls(ctxs, emb):
     """A batch of >= 20 000 codes from one caller is decoded as two pipelined halves on two engines (device -> host
     copies of the first under the kernels of the second: batcher.cu decode_batch_pipelined).  Ragged lengths so the cut
