@@ -647,7 +647,7 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
             mbar_wait(tfull_bar(acc), (it >> 1) & 1);
             tcgen05_fence_after();
 #pragma unroll 1
-            for (int c = cgrp; chunk_ok(t, c); c += EW, ++nch) {
+            for (int c = cgrp; chunk_ok(t, c) && !(a.dbg & 1); c += EW, ++nch) {
                 const int n = n0 + c * E::CW;
                 const int b = nch % EPI_NBUF;
                 const uint32_t buf = ebuf + b * E::BUF_BYTES;
@@ -916,6 +916,8 @@ void gemm_launch(const gemm_args & a, int num_sms, cudaStream_t st) {
         ncta = (c && std::atoi(c) == 1) ? 1 : 2;
     }
     gemm_args g = a;
+    static const int dbg = [] { const char * e = std::getenv("MIO_TTS_B200_GEMM_DBG"); return e ? std::atoi(e) : 0; }();
+    g.dbg = dbg;       // 1: timing experiment only -- epilogues release the accumulators without reading them (wrong results)
     g.reverse_m = traversal_reverse();
     if (a.epilogue == EPI_STORE32_LN) {
         if (a.N != 512 || a.taps != 1 || a.res == nullptr || a.ln_a == nullptr || a.ln_b == nullptr || (a.K % BLOCK_K) != 0 ||
