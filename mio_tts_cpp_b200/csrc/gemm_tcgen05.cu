@@ -51,7 +51,7 @@ template <int EPI> struct epi_cfg {
     static constexpr int CW = EPI == EPI_SWIGLU16 ? 64 : 32;
     static constexpr int ROW_BYTES = EPI == EPI_STORE32 ? 128 : 64;
     static constexpr int BUF_BYTES = 32 * ROW_BYTES;
-    static constexpr int ROPE_BYTES = EPI == EPI_ROPE16 ? 4096 : 0;      // (cos,sin) rows of the chunk, transposed
+    static constexpr int ROPE_BYTES = 0;      // (the (cos,sin) values of a row live in its thread's registers)
     static constexpr int WARP_BYTES = EPI_NBUF * BUF_BYTES + ROPE_BYTES;
 };
 
@@ -325,12 +325,10 @@ template <bool BF16> __device__ __forceinline__ uint32_t pack16t(float a, float 
 
 // 16-bit box of 32 columns (+ bias); ROPE rotates (even, odd) column pairs by this row's (cos, sin) from the staging tile
 template <bool ROPE, bool BIAS, bool BF16>
-__device__ __forceinline__ void chunk_store16(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, uint32_t rope_st,
+__device__ __forceinline__ void chunk_store16(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, const float4 (&rcs)[8],
                                               int lane, int n) {
     const uint32_t row = buf + lane * 64;
     const uint32_t sw = (uint32_t) ((lane >> 1) & 3) << 4;
-    const uint32_t rrow = rope_st + lane * 128;
-    const uint32_t rsw = (uint32_t) (lane & 7) << 4;
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
         float x[8];
@@ -360,7 +358,7 @@ __device__ __forceinline__ void chunk_store16(const gemm_args & a, const uint32_
         if constexpr (ROPE) {
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
-                const float4 cs = lds128(rrow + (((uint32_t) (2 * j + h) << 4) ^ rsw));   // (cos,sin) of 2 pairs
+                const float4 cs = rcs[2 * j + h];                                        // (cos,sin) of 2 pairs
                 const float x0 = x[4 * h], x1 = x[4 * h + 1], y0 = x[4 * h + 2], y1 = x[4 * h + 3];
                 x[4 * h] = x0 * cs.x - x1 * cs.y;
                 x[4 * h + 1] = x0 * cs.y + x1 * cs.x;
@@ -374,13 +372,13 @@ __device__ __forceinline__ void chunk_store16(const gemm_args & a, const uint32_
 }
 
 template <bool ROPE>
-__device__ __forceinline__ void chunk_store16_any(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, uint32_t rope_st,
+__device__ __forceinline__ void chunk_store16_any(const gemm_args & a, const uint32_t (&raw)[32], uint32_t buf, const float4 (&rcs)[8],
                                                   int lane, int n) {
     const bool bf16 = a.out_dtype == OP_BF16;   // warp-uniform
-    if (a.bias) { if (bf16) chunk_store16<ROPE, true, true>(a, raw, buf, rope_st, lane, n);
-                  else chunk_store16<ROPE, true, false>(a, raw, buf, rope_st, lane, n); }
-    else { if (bf16) chunk_store16<ROPE, false, true>(a, raw, buf, rope_st, lane, n);
-           else chunk_store16<ROPE, false, false>(a, raw, buf, rope_st, lane, n); }
+    if (a.bias) { if (bf16) chunk_store16<ROPE, true, true>(a, raw, buf, rcs, lane, n);
+                  else chunk_store16<ROPE, true, false>(a, raw, buf, rcs, lane, n); }
+    else { if (bf16) chunk_store16<ROPE, false, true>(a, raw, buf, rcs, lane, n);
+           else chunk_store16<ROPE, false, false>(a, raw, buf, rcs, lane, n); }
 }
 
 // SwiGLU: 32 accumulator columns (gate_j, up_j interleaved) -> 16 outputs = 16-byte slots 2*half, 2*half+1 of the row
@@ -543,7 +541,6 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
         const int ew = warp - 2;                     // epilogue warp index; column group = ew / 4
         const int cgrp = ew >> 2;
         const uint32_t ebuf = smem_base + C::STAGES * C::STAGE_BYTES + ew * E::WARP_BYTES;
-        const uint32_t rope_st = ebuf + EPI_NBUF * E::BUF_BYTES;
         auto rbar = [&](int b) { return bar_base + 256u + 8u * (ew * EPI_NBUF + b); };
         // in-place fp32 residual: either read back through TMA, added in registers and stored (has_res), or -- red_add --
         // left where it is and updated by a TMA reduce-add of the new term alone (no residual bytes cross L2 -> SM)
@@ -594,7 +591,7 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
             // per-row operands of this tile: the AdaLN gate vector of the row's utterance (STORE32), or the rope-table
             // rows this lane fetches for the transposed (cos,sin) staging (ROPE16: row (lane>>3)+4u, 16-byte slot lane&7)
             const float * gate_row = nullptr;
-            const float4 * rope_row[EPI == EPI_ROPE16 ? 8 : 1];
+            const float4 * rope_row = nullptr;           // ROPE16: this thread's row of the (cos, sin) table
             int utt_row = 0;
             if constexpr (EPI == EPI_STORE32) {
                 if (a.gate) gate_row = a.gate + (size_t) max(utt_next, 0) * a.gate_ld;
@@ -604,23 +601,26 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
             } else if constexpr (EPI == EPI_ROPE16) {
                 const int pos = max(pos_next, 0);
                 if (t + n_units < num_items) { const int r = tile_row0(t + n_units) + lane; pos_next = r < a.M ? __ldg(a.row_pos + r) : 0; }
-#pragma unroll
-                for (int u = 0; u < 8; ++u) {
-                    const int p = __shfl_sync(0xffffffffu, pos, (lane >> 3) + 4 * u);
-                    rope_row[u] = reinterpret_cast<const float4 *>(a.rope + (size_t) p * (a.head_dim >> 1)) + (lane & 7);
-                }
+                rope_row = reinterpret_cast<const float4 *>(a.rope + (size_t) pos * (a.head_dim >> 1));
             }
             const uint32_t taddr = tmem_base + ((uint32_t) (quad * 32) << 16) + acc * BN;
-            // RoPE: the (cos,sin) rows of a chunk are fetched one chunk ahead (the first before the accumulator wait),
-            // so their L2 latency hides behind the previous chunk's math instead of stalling every chunk
+            // RoPE: a thread owns a row, and the 16 (cos, sin) pairs of a 32-column chunk depend only on the row's position and
+            // on where the chunk sits inside its head -- with head_dim 64 and two column groups a warp's chunks of a tile all
+            // sit in the same half of a head, so the 128 bytes are read ONCE per tile (straight from the table: 4 full
+            // sectors per thread, L2-resident) and stay in registers; no staging tile, no shared-memory transpose.
             float4 cs[EPI == EPI_ROPE16 ? 8 : 1];
+            int cs_p0 = -1;
             auto rope_fetch = [&](int c) {
                 if constexpr (EPI == EPI_ROPE16) {
                     const int n = n0 + c * E::CW;
                     if (chunk_ok(t, c) && n < a.rope_cols) {
-                        const int p0 = (n % a.head_dim) >> 2;    // first pair of the chunk, in float4 (2-pair) units
+                        const int hd = a.head_dim;
+                        const int p0 = (((hd & (hd - 1)) == 0 ? (n & (hd - 1)) : (n % hd))) >> 2;   // first pair of the chunk, in float4 (2-pair) units
+                        if (p0 != cs_p0) {               // warp-uniform
+                            cs_p0 = p0;
 #pragma unroll
-                        for (int u = 0; u < 8; ++u) cs[u] = __ldg(rope_row[u] + p0);
+                            for (int u = 0; u < 8; ++u) cs[u] = __ldg(rope_row + p0 + u);
+                        }
                     }
                 }
             };
@@ -653,22 +653,14 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
                 const uint32_t buf = ebuf + b * E::BUF_BYTES;
                 uint32_t raw[32];
                 if constexpr (EPI == EPI_ROPE16) {
-                    // this chunk's (cos,sin) rows: coalesced global reads, transposed through the staging tile
                     const bool rotate = n < a.rope_cols;
                     tmem_ld_32x32b_x32(taddr + c * 32, raw);
-                    if (rotate) {
-#pragma unroll
-                        for (int u = 0; u < 8; ++u) {
-                            const int rr = (lane >> 3) + 4 * u;
-                            sts128(rope_st + rr * 128 + ((uint32_t) ((lane & 7) ^ (rr & 7)) << 4), cs[u]);
-                        }
-                    }
-                    rope_fetch(c + EW);
+                    rope_fetch(c);                       // a no-op unless the chunk sits elsewhere in its head than the last one
                     if (lane == 0) bulk_wait_read<EPI_NBUF - 1>();
                     __syncwarp();
                     tmem_ld_wait();
-                    if (rotate) chunk_store16_any<true>(a, raw, buf, rope_st, lane, n);
-                    else chunk_store16_any<false>(a, raw, buf, rope_st, lane, n);
+                    if (rotate) chunk_store16_any<true>(a, raw, buf, cs, lane, n);
+                    else chunk_store16_any<false>(a, raw, buf, cs, lane, n);
                 } else if constexpr (EPI == EPI_SWIGLU16) {
                     tmem_ld_32x32b_x32(taddr + c * 64, raw);
                     if (lane == 0) bulk_wait_read<EPI_NBUF - 1>();
@@ -690,7 +682,7 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
                     if (lane == 0) bulk_wait_read<EPI_NBUF - 1>();
                     __syncwarp();
                     tmem_ld_wait();
-                    chunk_store16_any<false>(a, raw, buf, 0, lane, n);
+                    { const float4 none[8] = {}; chunk_store16_any<false>(a, raw, buf, none, lane, n); }
                 } else {
                     tmem_ld_32x32b_x32(taddr + c * 32, raw);
                     if (has_res) mbar_wait(rbar(b), (nch / EPI_NBUF) & 1);       // residual box landed
