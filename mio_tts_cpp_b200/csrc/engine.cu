@@ -113,8 +113,11 @@ void engine::sync() { MIO_CUDA(cudaStreamSynchronize(st_)); }
 void engine::ensure(dbuf & b, size_t bytes) {
     if (bytes <= b.cap) return;
     MIO_CUDA(cudaStreamSynchronize(st_));
+    // first allocation: the request + 12.5 %; a buffer that has to grow again grows by at least half, so a server whose
+    // longest request creeps upward pays this (stream sync, free, malloc, clear, dropped tensor maps and graphs) O(log) times
+    const size_t regrow = b.p ? b.cap + b.cap / 2 : 0;
     if (b.p) { MIO_CUDA(cudaFree(b.p)); b.p = nullptr; b.cap = 0; }
-    const size_t cap = round_up(bytes + bytes / 8, 1 << 20);
+    const size_t cap = round_up(std::max(bytes + bytes / 8, regrow), 1 << 20);
     MIO_CUDA(cudaMalloc(&b.p, cap));
     MIO_CUDA(cudaMemsetAsync(b.p, 0, cap, st_));
     b.cap = cap;
