@@ -398,9 +398,9 @@ def aux_configs(m, peaks):
     out["config3_istft"] = {"frames": n_utt * frames, "n_fft": 1920, "hop": 480, "ms": ms, "frames_per_s": n_utt * frames / (ms * 1e-3),
                             "roofline": {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                                          "frac": gbs / peaks["hbm_gbs"]}}
-    # the frame size of the shipped 44.1 kHz checkpoints (n_fft 392 / hop 98: radix 4x7x7 fast path), and the generic
-    # kernel (any frame size; n_fft 400 / hop 100 has no fast path)
-    for key, nf, hp in (("istft_392_98", 392, 98), ("istft_generic_400_100", 400, 100)):
+    # the frame size of the shipped 44.1 kHz checkpoints (n_fft 392 / hop 98: radix 4x7x7 fast path), another fast-path
+    # size, and the generic kernel (any frame size; n_fft 1000 / hop 250 has no fast path)
+    for key, nf, hp in (("istft_392_98", 392, 98), ("istft_1024_256", 1024, 256), ("istft_generic_1000_250", 1000, 250)):
         ms_s, _ = m.istft_bench(1000, 1000, nf, hp, 5)
         b_s = (nf + 2) * 4 + hp * 4
         out[key] = {"frames": 1000000, "n_fft": nf, "hop": hp, "ms": ms_s, "frames_per_s": 1e6 / (ms_s * 1e-3),

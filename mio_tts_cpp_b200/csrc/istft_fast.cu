@@ -1,4 +1,5 @@
-// Fast path of the fused iSTFT for the common frame sizes (n_fft = 4*hop, n_fft/2 in {960, 1024, 640, 196}).
+// Fast path of the fused iSTFT for the common frame sizes (n_fft = 4*hop; n_fft in {1920, 2048, 1280, 392, 1024, 512, 800, 640,
+// 400, 960, 1200, 1600}: three Stockham passes of radix <= 16 each).
 //
 // Same math and summation order as istft.cu (see its header for the derivation and the reference lines,
 // /root/reference/src/mio-tts-lib.cpp:518-756), restructured for throughput:
@@ -117,6 +118,10 @@ template <> struct root_tab<16> {
     static constexpr float c[16] = {1.0f, 0.923879533f, 0.707106781f, 0.382683432f, 0.0f, -0.382683432f, -0.707106781f, -0.923879533f, -1.0f, -0.923879533f, -0.707106781f, -0.382683432f, 0.0f, 0.382683432f, 0.707106781f, 0.923879533f};
     static constexpr float s[16] = {0.0f, 0.382683432f, 0.707106781f, 0.923879533f, 1.0f, 0.923879533f, 0.707106781f, 0.382683432f, 0.0f, -0.382683432f, -0.707106781f, -0.923879533f, -1.0f, -0.923879533f, -0.707106781f, -0.382683432f};
 };
+template <> struct root_tab<8> {
+    static constexpr float c[8] = {1.0f, 0.707106781f, 0.0f, -0.707106781f, -1.0f, -0.707106781f, 0.0f, 0.707106781f};
+    static constexpr float s[8] = {0.0f, 0.707106781f, 1.0f, 0.707106781f, 0.0f, -0.707106781f, -1.0f, -0.707106781f};
+};
 template <> struct root_tab<15> {
     static constexpr float c[15] = {1.0f, 0.913545458f, 0.669130606f, 0.309016994f, -0.104528463f, -0.5f, -0.809016994f, -0.978147601f, -0.978147601f, -0.809016994f, -0.5f, -0.104528463f, 0.309016994f, 0.669130606f, 0.913545458f};
     static constexpr float s[15] = {0.0f, 0.406736643f, 0.743144825f, 0.951056516f, 0.994521895f, 0.866025404f, 0.587785252f, 0.207911691f, -0.207911691f, -0.587785252f, -0.866025404f, -0.994521895f, -0.951056516f, -0.743144825f, -0.406736643f};
@@ -156,6 +161,7 @@ template <int R1, int R2> __device__ __forceinline__ void dft_ct(float2 (&v)[R1 
 template <int R> __device__ __forceinline__ void dft_any(float2 (&v)[R]) {
     if constexpr (R <= 5 || R == 7) dft_small<R>(v);
     else if constexpr (R == 16) dft_ct<4, 4>(v);
+    else if constexpr (R == 8) dft_ct<2, 4>(v);
     else if constexpr (R == 15) dft_ct<3, 5>(v);
     else { static_assert(R == 10, "radix"); dft_ct<2, 5>(v); }
 }
@@ -163,7 +169,7 @@ template <int R> __device__ __forceinline__ void dft_any(float2 (&v)[R]) {
 // Shared-memory index of complex element i while a frame is between passes: one pad slot per 16 elements, so the
 // stride-R stores of the first pass (and the stride-16 ones after it) fall on distinct banks.
 __device__ __forceinline__ int padi(int i) { return i + (i >> 4); }
-template <int M> struct padded_len { static constexpr int value = M + (M >> 4); };
+template <int M> struct padded_len { static constexpr int value = (M + (M >> 4) + 1) & ~1; };   // even: 16-byte frame buffers
 
 // One in-place Stockham pass by one warp: reads x[j + q*m] (q < R), writes x[(j-k)*R + k + p*Ls], k = j % Ls.
 // All inputs of the pass sit in registers before the first store, so the pass runs in place; the LAST pass stores to
@@ -352,9 +358,10 @@ __global__ void __launch_bounds__(FW * 32, 16 / FW) istft_fast_kernel(const fast
         float * carry_out = s_carry + (cur ^ 1) * CARRY;
         // A thread keeps one 4-sample column r of the hop and walks the hops q = grp, grp + GROUPS, ...: its window
         // values hs[r + d*H] and its envelope are the same for every hop, so they are loaded once per round.
-        if constexpr (H % 4 != 0) {
-            // hop not a multiple of 4 (n_fft 392 / hop 98 of the 44.1 kHz checkpoints): two-sample columns; the crop
-            // (n_fft - hop) / 2 is odd there, so emitted samples are bounds-checked and stored one by one
+        if constexpr (H % 8 != 0) {
+            // the crop (n_fft - hop) / 2 = 3 hop / 2 is not a multiple of 4 (hop 98 of the 44.1 kHz checkpoints: 147; hop 100:
+            // 150), so 16-byte stores of emitted samples would be misaligned: two-sample columns, samples bounds-checked and
+            // stored one by one
             constexpr int H2 = H / 2, GROUPS = FTHREADS / H2;
             const int grp = threadIdx.x / H2, r = (threadIdx.x - grp * H2) * 2;
             if (grp < GROUPS) {
@@ -512,7 +519,10 @@ bool launch_istft_fast(const istft_plan & p, const float * spec, int pitch, cons
                        const long long * audio_off, float * audio, unsigned int * peak_bits, int n_utt, int max_frames,
                        cudaStream_t st) {
     if (p.hop * 4 != p.n_fft) return false;
-    if (p.n_fft != 1920 && p.n_fft != 2048 && p.n_fft != 1280 && p.n_fft != 392) return false;
+    switch (p.n_fft) {
+        case 1920: case 2048: case 1280: case 392: case 1024: case 512: case 800: case 640: case 400: case 960: case 1200: case 1600: break;
+        default: return false;
+    }
     fast_params P;
     P.n_freq = p.n_fft / 2 + 1;
     P.pad = (p.n_fft - p.hop) / 2;
@@ -522,11 +532,23 @@ bool launch_istft_fast(const istft_plan & p, const float * spec, int pitch, cons
     P.spec = spec; P.pitch = pitch; P.spec_row0 = spec_row0; P.n_frames = n_frames;
     P.audio_off = audio_off; P.audio = audio; P.peak_bits = peak_bits;
     P.scale = 1.0f / (float) P.n_freq;
+    // the other common STFT sizes (n_fft = 4 hop) run with 8 frames per CTA only: one instantiation each
+    switch (p.n_fft) {
+        case 392: launch_fast_t<8, 392, 4, 7, 7>(P, nullptr, n_utt, max_frames, st); return true;
+        case 1024: launch_fast_t<8, 1024, 16, 8, 4>(P, nullptr, n_utt, max_frames, st); return true;
+        case 512: launch_fast_t<8, 512, 16, 4, 4>(P, nullptr, n_utt, max_frames, st); return true;
+        case 800: launch_fast_t<8, 800, 16, 5, 5>(P, nullptr, n_utt, max_frames, st); return true;
+        case 640: launch_fast_t<8, 640, 16, 5, 4>(P, nullptr, n_utt, max_frames, st); return true;
+        case 400: launch_fast_t<8, 400, 10, 5, 4>(P, nullptr, n_utt, max_frames, st); return true;
+        case 960: launch_fast_t<8, 960, 16, 10, 3>(P, nullptr, n_utt, max_frames, st); return true;
+        case 1200: launch_fast_t<8, 1200, 15, 10, 4>(P, nullptr, n_utt, max_frames, st); return true;
+        case 1600: launch_fast_t<8, 1600, 16, 10, 5>(P, nullptr, n_utt, max_frames, st); return true;
+        default: break;
+    }
 #define MIO_ISTFT_CASE(FWV)                                                                               \
     switch (p.n_fft) {                                                                                    \
         case 1920: launch_fast_t<FWV, 1920, 16, 15, 4>(P, nullptr, n_utt, max_frames, st); break;          \
         case 2048: launch_fast_t<FWV, 2048, 16, 16, 4>(P, nullptr, n_utt, max_frames, st); break;          \
-        case 392: launch_fast_t<FWV, 392, 4, 7, 7>(P, nullptr, n_utt, max_frames, st); break;              \
         default: launch_fast_t<FWV, 1280, 16, 10, 4>(P, nullptr, n_utt, max_frames, st); break;           \
     }
     if (fw == 16) { MIO_ISTFT_CASE(16) } else if (fw == 4) { MIO_ISTFT_CASE(4) } else { MIO_ISTFT_CASE(8) }

@@ -72,7 +72,9 @@ def test_istft_vs_reference_fixture(name, ctxs):
     assert np.abs(a - z["audio"]).max() <= 2e-5      # what the fp32 kernels actually achieve (SFU exp/sincos fast path)
 
 
-@pytest.mark.parametrize("n_fft,hop", [(1920, 480), (392, 98), (120, 30), (2048, 512), (1280, 320), (64, 16), (30, 10)])
+@pytest.mark.parametrize("n_fft,hop", [(1920, 480), (392, 98), (120, 30), (2048, 512), (1280, 320), (64, 16), (30, 10),
+                                       (1024, 256), (512, 128), (800, 200), (640, 160), (400, 100), (960, 240), (1200, 300),
+                                       (1600, 400), (1000, 250), (1024, 128)])
 @pytest.mark.parametrize("frames", [1, 2, 3, 4, 7, 8, 9, 60, 61, 62, 64, 123, 200])
 def test_istft_vs_oracle_ragged(n_fft, hop, frames, ctxs):
     """Frame counts straddle the kernel's 8-frame rounds and its per-CTA chunk boundaries."""
