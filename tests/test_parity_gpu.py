@@ -420,12 +420,13 @@ def test_gemm_tail_split_is_bit_invariant(gguf_paths, emb):
     hashes = {}
     # "astat0": the A-stationary SwiGLU GEMM (gemm_astat.inc: A rows resident in shared memory, contiguous item ranges) off,
     # i.e. the gate/up projections on the generic kernel -- the same K order per element, so the same bits
-    for mode in ("0", "1", "2", None, "astat0"):
+    # "astat2": also the QKV + RoPE projections on the A-stationary kernel
+    for mode in ("0", "1", "2", None, "astat0", "astat2"):
         env = dict(os.environ)
         env.pop("MIO_TTS_B200_GEMM_SPLIT", None)
         env.pop("MIO_TTS_B200_GEMM_ASTAT", None)
-        if mode == "astat0":
-            env["MIO_TTS_B200_GEMM_ASTAT"] = "0"
+        if mode in ("astat0", "astat2"):
+            env["MIO_TTS_B200_GEMM_ASTAT"] = mode[-1]
         elif mode is not None:
             env["MIO_TTS_B200_GEMM_SPLIT"] = mode
         out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
