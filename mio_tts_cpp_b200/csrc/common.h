@@ -106,6 +106,7 @@ enum gemm_epilogue : int {
 struct gemm_args {
     CUtensorMap map_a;       // A: [rows, K] 16-bit, box 64 x 128, swizzle 128B
     CUtensorMap map_b;       // W: [N, taps*K] 16-bit, box 64 x gemm_w_box_rows(), swizzle 128B
+    CUtensorMap map_b_tail;  // the same tensor with gemm_w_tail_box_rows()-row boxes: the column sub-tiles of a split last wave
     CUtensorMap map_out;     // output (and in-place residual): box 32 x 32, swizzle 128B (fp32) / 64B (16-bit)
     int M, N, K, taps;       // K = reduction length PER TAP; W column of (tap, k) = tap*K + k
     // A coordinates of tap t:  row = tile row + tap_row0 + (t >> tap_shift),  column = a_col0 + (t & ((1<<tap_shift)-1)) * K.
@@ -153,7 +154,8 @@ CUtensorMap make_tmap_16(const void * ptr, uint64_t rows, uint64_t cols, uint32_
 // output tensor map: [rows, cols] of 2- or 4-byte elements, row pitch ld_elems (stores clip to rows x cols)
 CUtensorMap make_tmap_out(const void * ptr, uint64_t rows, uint64_t cols, uint64_t ld_elems, int elem_bytes);
 int gemm_block_n(int N);   // tile width the launcher will use for this N (weight rows are padded to it)
-int gemm_w_box_rows();      // rows per TMA box of a weight tensor map
+int gemm_w_box_rows();      // rows per TMA box of a weight tensor map (whole tiles)
+int gemm_w_tail_box_rows(); // ... of its second map (split-tail sub-tiles)
 
 // ---------------------------------------------------------------------------------------------
 // elementwise / normalisation kernels (ops.cu)

@@ -443,6 +443,7 @@ void engine::gemm(const dbuf & a, const dev_linear & w, int M, int epilogue, voi
     }
     g.map_a = amap(a, w.K);
     g.map_b = w.map_b;
+    g.map_b_tail = w.map_b_tail;
     g.map_out = omap(out, M, epilogue == EPI_SWIGLU16 ? w.N / 2 : w.N, ldo, (epilogue == EPI_STORE32 || epilogue == EPI_STORE32_LN) ? 4 : 2);
     g.M = M; g.N = w.N; g.K = w.K; g.taps = w.taps;
     g.tap_row0 = -(w.taps >> 1);   // k=3 "same" convolution over rows (taps == 1: plain GEMM)

@@ -42,7 +42,9 @@ namespace {
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;      // 16-bit elements -> 128-byte rows = one SWIZZLE_128B atom
 constexpr int UMMA_K = 16;
-constexpr int B_BOX_ROWS = 32;   // rows of W per TMA box: the narrowest split-tail sub-tile (BLOCK_N / 4) of a CTA pair takes one
+constexpr int B_BOX_ROWS = 128;      // rows of W per TMA box of a whole tile: ONE request per stage and CTA (with four 32-row boxes the
+                                     // producer's request rate, not the bytes, bounded the short-K shapes: QKV 82 -> 76 us, step -2 %)
+constexpr int B_TAIL_BOX_ROWS = 32;  // ... of a split-tail sub-tile (map_b_tail): the narrowest one (BLOCK_N / 4) of a CTA pair takes one
 constexpr uint32_t PEER_BIT_MASK = 0xFEFFFFFFu;   // clears the CTA-pair rank bit of a shared::cluster address
 constexpr int EPI_NBUF = 3;      // output boxes per epilogue warp (residual prefetch distance = 2 chunks)
 
@@ -475,7 +477,10 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
             uint32_t kit = 0;
             for (int t = unit; t < num_items; t += n_units) {
                 const int b_rows = item_width(t) / NCTA;               // W rows this CTA stages for the item
-                const int n_boxes = b_rows / B_BOX_ROWS;
+                const bool tail_item = t >= split_from && split_shift > 0;
+                const int box_rows = tail_item ? B_TAIL_BOX_ROWS : B_BOX_ROWS;
+                const CUtensorMap * wmap = tail_item ? &a.map_b_tail : &a.map_b;
+                const int n_boxes = b_rows / box_rows;
                 const uint32_t stage_tx = C::A_BYTES + b_rows * BLOCK_K * 2;
                 const int m0 = item_m0(t) + cta_rank * BLOCK_M;
                 const int n0 = item_n0(t) + cta_rank * b_rows;
@@ -490,14 +495,14 @@ __global__ void __launch_bounds__(64 + 128 * EW, 1) gemm_tcgen05_kernel(const __
                             mbar_expect_tx(full_bar(s), stage_tx);
                             tma_load_2d(sa, &a.map_a, full_bar(s), acol + kb * BLOCK_K, arow);
                             for (int bx = 0; bx < n_boxes; ++bx)
-                                tma_load_2d(sa + C::A_BYTES + bx * (B_BOX_ROWS * BLOCK_K * 2), &a.map_b, full_bar(s),
-                                            tap * a.K + kb * BLOCK_K, n0 + bx * B_BOX_ROWS);
+                                tma_load_2d(sa + C::A_BYTES + bx * (box_rows * BLOCK_K * 2), wmap, full_bar(s),
+                                            tap * a.K + kb * BLOCK_K, n0 + bx * box_rows);
                         } else {
                             if (cta_rank == 0) mbar_expect_tx(full_bar(s), 2 * stage_tx);   // both CTAs' bytes
                             tma_load_2d_pair(sa, &a.map_a, full_bar(s), acol + kb * BLOCK_K, arow);
                             for (int bx = 0; bx < n_boxes; ++bx)
-                                tma_load_2d_pair(sa + C::A_BYTES + bx * (B_BOX_ROWS * BLOCK_K * 2), &a.map_b, full_bar(s),
-                                                 tap * a.K + kb * BLOCK_K, n0 + bx * B_BOX_ROWS);
+                                tma_load_2d_pair(sa + C::A_BYTES + bx * (box_rows * BLOCK_K * 2), wmap, full_bar(s),
+                                                 tap * a.K + kb * BLOCK_K, n0 + bx * box_rows);
                         }
                     }
                 }
@@ -791,11 +796,11 @@ int tail_split_shift(int tiles, int units, int bn, int ncta) {
     float best_cost = 1.0f;
     for (int sh = 1; sh <= 2; ++sh) {
         const int s = 1 << sh;
-        if ((bn >> sh) / ncta < B_BOX_ROWS || (bn >> sh) < 64) break;
+        if ((bn >> sh) / ncta < B_TAIL_BOX_ROWS || (bn >> sh) < 64) break;
         const float cost = (float) ((r * s + units - 1) / units) * (0.25f + 0.75f / (float) s);
         if (cost < best_cost - 0.05f) { best_cost = cost; best = sh; }
     }
-    if (mode > 0 && mode <= 2) best = ((bn >> mode) / ncta >= B_BOX_ROWS && (bn >> mode) >= 64) ? mode : 0;   // forced (tests)
+    if (mode > 0 && mode <= 2) best = ((bn >> mode) / ncta >= B_TAIL_BOX_ROWS && (bn >> mode) >= 64) ? mode : 0;   // forced (tests)
     return best;
 }
 
@@ -859,6 +864,7 @@ bool pdl_enabled() {
 
 int gemm_block_n(int N) { return N >= 256 ? 256 : 128; }
 int gemm_w_box_rows() { return B_BOX_ROWS; }
+int gemm_w_tail_box_rows() { return B_TAIL_BOX_ROWS; }
 
 CUtensorMap make_tmap_16(const void * ptr, uint64_t rows, uint64_t cols, uint32_t box_rows) {
     if ((cols % 8) != 0) throw cuda_error("tensor map: row pitch must be a multiple of 16 bytes");

@@ -85,6 +85,7 @@ struct loader {
         MIO_CUDA(cudaMemset(L.w16, 0, n_pad * (size_t) taps * K * 2));
         MIO_CUDA(cudaMemcpy(L.w16, h.data(), h.size() * 2, cudaMemcpyHostToDevice));
         L.map_b = make_tmap_16(L.w16, (uint64_t) N, (uint64_t) taps * K, (uint32_t) gemm_w_box_rows());
+        L.map_b_tail = make_tmap_16(L.w16, (uint64_t) N, (uint64_t) taps * K, (uint32_t) gemm_w_tail_box_rows());
         if (bias) {
             std::vector<float> bp(((size_t) N + 3) / 4 * 4, 0.0f);
             std::copy(bias->begin(), bias->end(), bp.begin());

@@ -29,7 +29,7 @@ struct dev_linear {
     float * bias = nullptr;     // [N] or null
     int N = 0, K = 0, taps = 1;
     int dtype = OP_BF16;
-    CUtensorMap map_b;
+    CUtensorMap map_b, map_b_tail;   // 128-row boxes (whole tiles) / 32-row boxes (split-tail sub-tiles)
 };
 
 struct dev_norm { float * w = nullptr; float * b = nullptr; };

@@ -55,6 +55,7 @@ void refmodel::make_linear(dev_linear & L, const std::vector<float> & rows, int 
     MIO_CUDA(cudaMemset(L.w16, 0, n_pad * (size_t) taps * K * 2));
     MIO_CUDA(cudaMemcpy(L.w16, h.data(), h.size() * 2, cudaMemcpyHostToDevice));
     L.map_b = make_tmap_16(L.w16, (uint64_t) N, (uint64_t) taps * K, (uint32_t) gemm_w_box_rows());
+    L.map_b_tail = make_tmap_16(L.w16, (uint64_t) N, (uint64_t) taps * K, (uint32_t) gemm_w_tail_box_rows());
     if (bias) {
         std::vector<float> bp(((size_t) N + 3) / 4 * 4, 0.0f);
         std::copy(bias->begin(), bias->end(), bp.begin());
@@ -347,6 +348,7 @@ void refenc::gemm(const void * a, uint64_t a_width, uint64_t a_rows, const dev_l
     std::memset(&g, 0, sizeof(g));
     g.map_a = amap(a, a_width, a_rows);
     g.map_b = w.map_b;
+    g.map_b_tail = w.map_b_tail;
     g.map_out = omap(out, M, out_cols, ldo, epilogue == EPI_STORE32 ? 4 : 2);
     g.M = M; g.N = w.N; g.K = w.K; g.taps = w.taps;
     g.tap_row0 = o.tap_row0; g.tap_shift = o.tap_shift; g.a_col0 = o.a_col0; g.act = o.act;
