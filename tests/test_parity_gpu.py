@@ -418,14 +418,13 @@ def test_gemm_tail_split_is_bit_invariant(gguf_paths, emb):
         "print('HASH', h.hexdigest())\n"
     ) % (ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "tests", "golden", "en_female_emb.npy"), path)
     hashes = {}
-    # "astat0": the A-stationary SwiGLU GEMM (gemm_astat.inc: A rows resident in shared memory, contiguous item ranges) off,
-    # i.e. the gate/up projections on the generic kernel -- the same K order per element, so the same bits
-    # "astat2": also the QKV + RoPE projections on the A-stationary kernel
-    for mode in ("0", "1", "2", None, "astat0", "astat2"):
+    # "astat1" / "astat2": the gate/up (and QKV + RoPE) projections on the A-stationary GEMM (gemm_astat.inc: A rows resident in
+    # shared memory, contiguous item ranges; off by default) -- the same K order per element, so the same bits
+    for mode in ("0", "1", "2", None, "astat1", "astat2"):
         env = dict(os.environ)
         env.pop("MIO_TTS_B200_GEMM_SPLIT", None)
         env.pop("MIO_TTS_B200_GEMM_ASTAT", None)
-        if mode in ("astat0", "astat2"):
+        if mode in ("astat1", "astat2"):
             env["MIO_TTS_B200_GEMM_ASTAT"] = mode[-1]
         elif mode is not None:
             env["MIO_TTS_B200_GEMM_SPLIT"] = mode
